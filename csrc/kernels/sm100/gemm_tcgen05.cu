@@ -1,0 +1,468 @@
+// Persistent, warp-specialised tcgen05 GEMM for sm_100a.
+//
+//   C[b] = epilogue( alpha * A[b] x B[b]^T )        A: [M,K]   B: [N,K]   C: [M,N] row-major
+//
+// Each operand may be stored K-major (reduction dim contiguous) or MN-major (M resp. N
+// contiguous), so one kernel serves the three GEMMs of a linear layer without transposes:
+//   forward  y  = x  W^T   (A K-major,  B K-major)
+//   dgrad    dx = dy W     (A K-major,  B MN-major)
+//   wgrad    dW = dy^T x   (A MN-major, B MN-major; fp32 accumulate into the grad buffer)
+// and the two batched GEMMs of attention (QK^T, PV).
+//
+// Structure: warp 0 = TMA producer, warp 1 = MMA issuer (single thread, tcgen05.mma with the
+// accumulator in TMEM), warp 2 = TMEM allocator, warps 4-7 = epilogue (tcgen05.ld -> registers ->
+// fused bias / GELU / dGELU / residual / cast -> global).  The accumulator is double-buffered in
+// TMEM (2 x BLOCK_N columns) so the epilogue of tile i overlaps the main loop of tile i+1.
+//
+// Replaces the reference's cuBLAS calls (reference smdistributed/modelparallel/torch/nn/
+// transformer.py:1107-1134,1476-1482,1515,1657,1810-1812; nn/linear.py:62) and its TorchScript
+// bias-GELU (nn/gelu.py:28-47), which becomes a GEMM epilogue here.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+using namespace smp100;
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;  // 64 x 2 B = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 256;
+constexpr int EPI_WARP0 = 4;  // epilogue warps 4..7 (warp_idx % 4 selects the TMEM lane quarter)
+constexpr int GROUP_M = 8;    // L2-friendly raster: 8 m-blocks share one sweep over n
+
+enum EpiMode : int { EPI_NONE = 0, EPI_GELU_TANH = 1, EPI_GELU_ERF = 2, EPI_DGELU_TANH = 3, EPI_DGELU_ERF = 4 };
+
+struct GemmParams {
+  int M, N, K, batch;
+  int num_m, num_n, num_k;
+  int a_mn_major, b_mn_major;
+  // output
+  void* C;
+  int ldc;
+  long long c_bs;
+  int out_dtype;
+  // optional pre-activation output (EPI_GELU_*)
+  void* aux;
+  // optional residual / accumulate input or dGELU pre-activation input
+  const void* R;
+  int ldr;
+  long long r_bs;
+  int r_dtype;
+  // optional bias over N
+  const void* bias;
+  int bias_dtype;
+  float alpha, beta;
+  int epi;
+  uint32_t idesc;
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
+  static constexpr int B_BYTES = BN * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (power of two >= 32)
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ void tile_coords(int t, const GemmParams& p, int& b, int& m_blk, int& n_blk) {
+  const int per_batch = p.num_m * p.num_n;
+  b = t / per_batch;
+  const int r = t - b * per_batch;
+  const int group_size = GROUP_M * p.num_n;
+  const int group_id = r / group_size;
+  const int first_m = group_id * GROUP_M;
+  const int gsm = min(p.num_m - first_m, GROUP_M);
+  const int in_group = r - group_id * group_size;
+  m_blk = first_m + in_group % gsm;
+  n_blk = in_group / gsm;
+}
+
+template <typename T>
+__device__ __forceinline__ void load32(const T* __restrict__ ptr, float (&o)[32], bool vec, int nvalid) {
+  if (vec) {
+    constexpr int PER = 16 / sizeof(T);
+    constexpr int NV = 32 / PER;
+    const uint4* p4 = reinterpret_cast<const uint4*>(ptr);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      uint4 raw = p4[i];
+      const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+      for (int j = 0; j < PER; ++j) o[i * PER + j] = smpk::to_f32<T>(e[j]);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) o[i] = (i < nvalid) ? smpk::to_f32<T>(ptr[i]) : 0.f;
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ void store32(T* __restrict__ ptr, const float (&v)[32], bool vec, int nvalid) {
+  if (vec) {
+    constexpr int PER = 16 / sizeof(T);
+    constexpr int NV = 32 / PER;
+    uint4* p4 = reinterpret_cast<uint4*>(ptr);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      uint4 raw;
+      T* e = reinterpret_cast<T*>(&raw);
+#pragma unroll
+      for (int j = 0; j < PER; ++j) e[j] = smpk::from_f32<T>(v[i * PER + j]);
+      p4[i] = raw;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < nvalid) ptr[i] = smpk::from_f32<T>(v[i]);
+  }
+}
+
+__device__ __forceinline__ void load32_dyn(const void* base, int dtype, long long off, float (&o)[32], bool vec,
+                                           int nvalid) {
+  if (dtype == SMPK_F32)
+    load32<float>(reinterpret_cast<const float*>(base) + off, o, vec, nvalid);
+  else if (dtype == SMPK_BF16)
+    load32<__nv_bfloat16>(reinterpret_cast<const __nv_bfloat16*>(base) + off, o, vec, nvalid);
+  else
+    load32<__half>(reinterpret_cast<const __half*>(base) + off, o, vec, nvalid);
+}
+__device__ __forceinline__ void store32_dyn(void* base, int dtype, long long off, const float (&v)[32], bool vec,
+                                            int nvalid) {
+  if (dtype == SMPK_F32)
+    store32<float>(reinterpret_cast<float*>(base) + off, v, vec, nvalid);
+  else if (dtype == SMPK_BF16)
+    store32<__nv_bfloat16>(reinterpret_cast<__nv_bfloat16*>(base) + off, v, vec, nvalid);
+  else
+    store32<__half>(reinterpret_cast<__half*>(base) + off, v, vec, nvalid);
+}
+
+template <int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+    gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                        const GemmParams p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* full_bar = bars;                   // [STAGES]  TMA -> MMA
+  uint64_t* empty_bar = bars + C::STAGES;      // [STAGES]  MMA -> TMA
+  uint64_t* tfull_bar = bars + 2 * C::STAGES;  // [2]       MMA -> epilogue
+  uint64_t* tempty_bar = tfull_bar + 2;        // [2]       epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < C::STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], 4);  // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc<C::TMEM_COLS>(tmem_slot);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_tiles = p.batch * p.num_m * p.num_n;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        int b, m_blk, n_blk;
+        tile_coords(t, p, b, m_blk, n_blk);
+        const int m0 = m_blk * BLOCK_M, n0 = n_blk * BN;
+        for (int kb = 0; kb < p.num_k; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * C::STAGE_BYTES;
+          uint8_t* sb = sa + C::A_BYTES;
+          mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+          const int k0 = kb * BLOCK_K;
+          if (!p.a_mn_major) {
+            tma_load_3d(sa, &tma_a, &full_bar[stage], k0, m0, b);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BLOCK_M / 64; ++j)
+              tma_load_3d(sa + j * (BLOCK_K * 128), &tma_a, &full_bar[stage], m0 + j * 64, k0, b);
+          }
+          if (!p.b_mn_major) {
+            tma_load_3d(sb, &tma_b, &full_bar[stage], k0, n0, b);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_3d(sb + j * (BLOCK_K * 128), &tma_b, &full_bar[stage], n0 + j * 64, k0, b);
+          }
+          if (++stage == C::STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer
+    if (lane == 0) {
+      // K-major: 8-row groups 1024 B apart.  MN-major: K rows 128 B apart inside a 64-wide atom,
+      // 8-row groups 1024 B apart, atoms BLOCK_K*128 B apart.
+      const uint64_t hi_a = p.a_mn_major ? make_smem_desc_hi(BLOCK_K * 128, 1024) : make_smem_desc_hi(16, 1024);
+      const uint64_t hi_b = p.b_mn_major ? make_smem_desc_hi(BLOCK_K * 128, 1024) : make_smem_desc_hi(16, 1024);
+      // per-UMMA_K advance of the start-address field (16-byte units)
+      const uint32_t adv_a = p.a_mn_major ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+      const uint32_t adv_b = p.b_mn_major ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < p.num_k; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          uint8_t* sa = smem + stage * C::STAGE_BYTES;
+          uint8_t* sb = sa + C::A_BYTES;
+          const uint64_t da = make_smem_desc(sa, hi_a);
+          const uint64_t db = make_smem_desc(sb, hi_b);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            umma_f16(tmem_d, da + uint64_t(k * adv_a), db + uint64_t(k * adv_b), p.idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          if (++stage == C::STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= EPI_WARP0) {
+    // ===================================================================== epilogue
+    const int ew = warp - EPI_WARP0;  // == warp % 4: TMEM lanes [32*ew, 32*ew+32)
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const int out_es = (p.out_dtype == SMPK_F32) ? 4 : 2;
+    const bool c_vec_ok = ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0) && ((p.ldc * out_es) % 16 == 0) &&
+                          ((p.c_bs * out_es) % 16 == 0) &&
+                          (p.aux == nullptr || (reinterpret_cast<uintptr_t>(p.aux) & 15) == 0);
+    const int r_es = (p.r_dtype == SMPK_F32) ? 4 : 2;
+    const bool r_vec_ok = p.R == nullptr || (((reinterpret_cast<uintptr_t>(p.R) & 15) == 0) &&
+                                             ((p.ldr * r_es) % 16 == 0) && ((p.r_bs * r_es) % 16 == 0));
+    const int b_es = (p.bias_dtype == SMPK_F32) ? 4 : 2;
+    const bool bias_vec_ok = p.bias == nullptr || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
+    (void)b_es;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      int b, m_blk, n_blk;
+      tile_coords(t, p, b, m_blk, n_blk);
+      const int row = m_blk * BLOCK_M + ew * 32 + lane;
+      const int n0 = n_blk * BN;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (uint32_t(ew * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t raw[32];
+        tmem_ld_32x32(taddr + c * 32, raw);
+        tmem_ld_wait();
+        const int col0 = n0 + c * 32;
+        const int nvalid = min(32, p.N - col0);
+        if (row < p.M && nvalid > 0) {
+          const bool full = nvalid == 32;
+          float v[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]) * p.alpha;
+          if (p.bias != nullptr) {
+            float bv[32];
+            load32_dyn(p.bias, p.bias_dtype, col0, bv, full && bias_vec_ok, nvalid);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] += bv[i];
+          }
+          const long long coff = (long long)b * p.c_bs + (long long)row * p.ldc + col0;
+          if (p.R != nullptr) {
+            float rv[32];
+            const long long roff = (long long)b * p.r_bs + (long long)row * p.ldr + col0;
+            load32_dyn(p.R, p.r_dtype, roff, rv, full && r_vec_ok, nvalid);
+            if (p.epi == EPI_DGELU_TANH) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] *= smpk::gelu_tanh_grad(rv[i]);
+            } else if (p.epi == EPI_DGELU_ERF) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] *= smpk::gelu_erf_grad(rv[i]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] += p.beta * rv[i];
+            }
+          }
+          if (p.epi == EPI_GELU_TANH || p.epi == EPI_GELU_ERF) {
+            if (p.aux != nullptr) store32_dyn(p.aux, p.out_dtype, coff, v, full && c_vec_ok, nvalid);
+            if (p.epi == EPI_GELU_TANH) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = smpk::gelu_tanh(v[i]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = smpk::gelu_erf(v[i]);
+            }
+          }
+          store32_dyn(p.C, p.out_dtype, coff, v, full && c_vec_ok, nvalid);
+        }
+      }
+      // all TMEM reads of this accumulator stage are done -> hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<C::TMEM_COLS>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(sym);
+  return fn;
+}
+
+// Operand tensor map.  K-major: dims {K, rows, batch}, box {64, box_rows, 1}.
+// MN-major: dims {rows(MN), K, batch}, box {64, BLOCK_K, 1}.
+int make_operand_map(CUtensorMap* map, int in_dtype, const void* ptr, int rows, int K, int batch, int ld,
+                     long long bs, bool mn_major, int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return smpk::set_error("cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t dims[3];
+  cuuint64_t strides[2];
+  cuuint32_t box[3];
+  cuuint32_t estr[3] = {1, 1, 1};
+  if (!mn_major) {
+    dims[0] = (cuuint64_t)K;
+    dims[1] = (cuuint64_t)rows;
+    box[0] = BLOCK_K;
+    box[1] = (cuuint32_t)box_rows;
+  } else {
+    dims[0] = (cuuint64_t)rows;
+    dims[1] = (cuuint64_t)K;
+    box[0] = 64;
+    box[1] = BLOCK_K;
+  }
+  dims[2] = (cuuint64_t)batch;
+  box[2] = 1;
+  strides[0] = (cuuint64_t)ld * 2;
+  strides[1] = (cuuint64_t)(batch > 1 ? bs : (long long)dims[1] * ld) * 2;
+  if (strides[1] == 0) strides[1] = strides[0];
+  CUtensorMapDataType dt = in_dtype == SMPK_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUresult r = enc(map, dt, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return smpk::set_error("cuTensorMapEncodeTiled failed (%d): rows=%d K=%d batch=%d ld=%d bs=%lld mn_major=%d", (int)r,
+                           rows, K, batch, ld, bs, (int)mn_major);
+  return 0;
+}
+
+template <int BN>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream, int max_ctas) {
+  using C = Cfg<BN>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    SMPK_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         C::SMEM_BYTES));
+    attr_set[dev & 63] = true;
+  }
+  p.num_n = (p.N + BN - 1) / BN;
+  p.idesc = make_idesc_f16(/*fmt filled by caller in idesc low bits*/ p.idesc, p.a_mn_major, p.b_mn_major, BLOCK_M, BN);
+  const int total = p.batch * p.num_m * p.num_n;
+  int grid = smpk::num_sms();
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (total < grid) grid = total;
+  gemm_tcgen05_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+  SMPK_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+// See include/smpb200_kernels.h for the contract.
+SMPK_API int smpk_gemm(void* stream, int in_dtype, int out_dtype, int M, int N, int K, int batch, const void* A,
+                       int lda, long long a_bs, int a_mn_major, const void* B, int ldb, long long b_bs,
+                       int b_mn_major, void* C, int ldc, long long c_bs, const void* bias, int bias_dtype,
+                       const void* R, int ldr, long long r_bs, int r_dtype, void* aux, float alpha, float beta,
+                       int epi, int max_ctas) {
+  SMPK_REQUIRE(in_dtype == SMPK_BF16 || in_dtype == SMPK_F16, "smpk_gemm: inputs must be bf16 or fp16");
+  SMPK_REQUIRE(M > 0 && N > 0 && K > 0 && batch > 0, "smpk_gemm: empty problem M=%d N=%d K=%d batch=%d", M, N, K, batch);
+  SMPK_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && (a_bs % 8) == 0 && (b_bs % 8) == 0,
+               "smpk_gemm: TMA needs 16-byte aligned strides (lda=%d ldb=%d a_bs=%lld b_bs=%lld)", lda, ldb, a_bs, b_bs);
+  SMPK_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "smpk_gemm: operand pointers must be 16-byte aligned");
+  SMPK_REQUIRE(epi >= 0 && epi <= 4, "smpk_gemm: bad epilogue mode %d", epi);
+  SMPK_REQUIRE(!(epi >= 3) || R != nullptr, "smpk_gemm: dGELU epilogue needs the pre-activation in R");
+
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = M; p.N = N; p.K = K; p.batch = batch;
+  p.num_m = (M + BLOCK_M - 1) / BLOCK_M;
+  p.num_k = (K + BLOCK_K - 1) / BLOCK_K;
+  p.a_mn_major = a_mn_major ? 1 : 0;
+  p.b_mn_major = b_mn_major ? 1 : 0;
+  p.C = C; p.ldc = ldc; p.c_bs = c_bs; p.out_dtype = out_dtype;
+  p.aux = aux;
+  p.R = R; p.ldr = ldr; p.r_bs = r_bs; p.r_dtype = r_dtype;
+  p.bias = bias; p.bias_dtype = bias_dtype;
+  p.alpha = alpha; p.beta = beta; p.epi = epi;
+  p.idesc = (in_dtype == SMPK_BF16) ? 1u : 0u;  // format code, expanded in launch<>
+
+  const int BN = (N > 128) ? 256 : (N > 64 ? 128 : 64);
+  CUtensorMap ta, tb;
+  int rc = make_operand_map(&ta, in_dtype, A, M, K, batch, lda, a_bs, p.a_mn_major, BLOCK_M);
+  if (rc) return rc;
+  rc = make_operand_map(&tb, in_dtype, B, N, K, batch, ldb, b_bs, p.b_mn_major, BN);
+  if (rc) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (BN == 256) return launch<256>(ta, tb, p, s, max_ctas);
+  if (BN == 128) return launch<128>(ta, tb, p, s, max_ctas);
+  return launch<64>(ta, tb, p, s, max_ctas);
+}

@@ -1,0 +1,114 @@
+/* C ABI of libsmpb200_kernels.so - the sm_100a kernel library of smdistributed_modelparallel_b200.
+ *
+ * Conventions
+ *  - every entry point returns 0 on success and non-zero on failure; smpk_last_error() then holds a
+ *    thread-local description.
+ *  - `stream` is a cudaStream_t passed as void*.  Nothing synchronises the device.
+ *  - dtype codes: 0 = float32, 1 = float16, 2 = bfloat16.
+ *  - no entry point allocates device memory; scratch buffers are supplied by the caller and their
+ *    sizes are reported by the *_scratch_floats helpers.
+ *
+ * Where an entry point replaces a native function of the reference wheel the comment cites the
+ * reference call site (paths relative to smdistributed/modelparallel/).
+ */
+#ifndef SMPB200_KERNELS_H_
+#define SMPB200_KERNELS_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* smpk_last_error(void);
+int smpk_version(void);
+int smpk_device_cc(void);
+
+/* ---- tcgen05 GEMM ------------------------------------------------------------------------------
+ * C[b] = epilogue(alpha * A[b] (MxK) * B[b]^T (NxK)),  b in [0, batch).
+ * a_mn_major / b_mn_major = 0: operand stored K-major (row = M resp. N index, K contiguous, ld = row
+ * stride);  = 1: stored MN-major (row = K index, M resp. N contiguous).  Strides are in elements and
+ * must be multiples of 8; inputs are bf16 or fp16, the accumulator is fp32 in tensor memory.
+ * Epilogue, in order: + bias[N] ; epi 0: + beta * R ; epi 1/2: aux = value (optional), value =
+ * gelu_tanh / gelu_erf(value) ; epi 3/4: value *= gelu_tanh' / gelu_erf'(R).  R may alias C
+ * (in-place accumulate).  max_ctas > 0 caps the persistent grid (to leave SMs to a side stream).
+ * Replaces cuBLAS calls at torch/nn/transformer.py:1107-1134,1476-1482,1515,1657,1810-1812 and the
+ * TorchScript bias-GELU at torch/nn/gelu.py:28-47. */
+int smpk_gemm(void* stream, int in_dtype, int out_dtype, int M, int N, int K, int batch, const void* A, int lda,
+              long long a_bs, int a_mn_major, const void* B, int ldb, long long b_bs, int b_mn_major, void* C, int ldc,
+              long long c_bs, const void* bias, int bias_dtype, const void* R, int ldr, long long r_bs, int r_dtype,
+              void* aux, float alpha, float beta, int epi, int max_ctas);
+
+/* ---- LayerNorm (Apex fused_layer_norm_cuda: torch/apex/normalization/fused_layer_norm.py:26-78) */
+int smpk_layernorm_fwd(void* stream, const void* x, const void* residual, void* sum_out, int x_dtype,
+                       const void* gamma, const void* beta, int w_dtype, void* y, int y_dtype, float* mean, float* rstd,
+                       int rows, int H, float eps);
+/* number of partial-sum slots the backward uses; scratch must hold 2 * grid * H floats */
+int smpk_ln_bwd_grid(int rows, int H);
+int smpk_layernorm_bwd(void* stream, const void* dy, int dy_dtype, const void* x, int x_dtype, const float* mean,
+                       const float* rstd, const void* gamma, int w_dtype, void* dx, int dx_dtype, const void* dx_add,
+                       void* dgamma, void* dbeta, int accumulate_wgrad, float* scratch, int rows, int H);
+/* hidden-sharded LayerNorm phases (smp_torch_cuda_lib forward_affine_mean_var / backward_affine_local_sums /
+ * backward_affine_finish: torch/nn/layer_norm.py:52-81) */
+int smpk_ln_partial_stats(void* stream, const void* x, int x_dtype, float* stats, int rows, int H);
+int smpk_ln_apply_stats(void* stream, const void* x, int x_dtype, const float* mean, const float* rstd,
+                        const void* gamma, const void* beta, int w_dtype, void* y, int y_dtype, int rows, int H);
+int smpk_ln_bwd_local_sums(void* stream, const void* dy, int dy_dtype, const void* x, int x_dtype, const float* mean,
+                           const float* rstd, const void* gamma, int w_dtype, float* sums, int rows, int H);
+int smpk_ln_bwd_finish(void* stream, const void* dy, int dy_dtype, const void* x, int x_dtype, const float* mean,
+                       const float* rstd, const void* gamma, int w_dtype, const float* sums, void* dx, int dx_dtype,
+                       int rows, int H, int H_total);
+
+/* ---- softmax (smp_torch_cuda_lib scaled_*_softmax_*: torch/nn/softmax.py:7-12,40-93)
+ * mode 0: plain, 1: causal, 2: uint8 mask [batch,1,Sq,Sk] (non-zero = masked). */
+int smpk_softmax_fwd(void* stream, const void* x, void* y, int dtype, const void* mask, int mode, float scale,
+                     int batch_heads, int heads, int Sq, int Sk);
+int smpk_softmax_bwd(void* stream, const void* dy, const void* y, void* dx, int dtype, int causal, float scale,
+                     int batch_heads, int Sq, int Sk);
+int smpk_get_batch_per_block(int sq, int sk, int b, int np);
+
+/* ---- vocab-parallel cross entropy (torch/nn/cross_entropy.py:28-98) */
+int smpk_ce_stats(void* stream, const void* logits, int dtype, const long long* targets, long long vocab_start,
+                  int rows, int V, long long ld, float* row_max, float* row_sum, float* row_tgt);
+int smpk_ce_finish(void* stream, void* logits, int dtype, const long long* targets, long long vocab_start, int rows,
+                   int V, long long ld, const float* gmax, const float* gsum, const float* gtgt, float grad_scale,
+                   long long ignore_index, float* loss, int write_grad);
+
+/* ---- elementwise / layout (torch/nn/gelu.py:28-47; torch/nn/transformer.py:114-163,1565-1615) */
+int smpk_bias_gelu(void* stream, const void* x, const void* bias, int bias_dtype, const void* dy, void* out, int dtype,
+                   long long rows, int N, int mode, int backward);
+int smpk_colsum_scratch_floats(int N);
+int smpk_colsum(void* stream, const void* x, int dtype, int rows, int N, long long ld, void* out, int out_dtype,
+                int accumulate, float* scratch);
+int smpk_qkv_rotary(void* stream, void* fused, void* q, void* k, void* v, int dtype, const float* cosT,
+                    const float* sinT, int B, int S, int heads, int d, int rot, int style, int pos_offset, int merge,
+                    long long fused_ld);
+int smpk_head_transpose(void* stream, const void* src, void* dst, int dtype, int B, int S, int heads, int d,
+                        int to_heads_first);
+
+/* ---- multi-tensor apply (amp_C: torch/fp16/fp16.py:132,159,555; torch/apex/optimizers/*.py)
+ * lists: array of `depth` pointers, each to an array of n device addresses; sizes: n element counts;
+ * dtypes: one code per list; chunk: elements per thread block. noop (device int, optional): skip
+ * the whole launch when non-zero.  flag (device int): set to 1 when a non-finite input is seen. */
+#define SMPK_MT_ARGS void *stream, int n, void *const *const *lists, const long long *sizes, const int *dtypes, int chunk
+int smpk_mt_scale(SMPK_MT_ARGS, float scale, const float* scale_dev, int* flag, const int* noop);
+int smpk_mt_axpby(SMPK_MT_ARGS, float a, float b, int check, int* flag, const int* noop);
+int smpk_mt_adam(SMPK_MT_ARGS, int depth, float lr, float beta1, float beta2, float eps, int step, int adamw,
+                 int bias_correction, float wd, float grad_scale, const float* grad_scale_dev, const int* noop);
+int smpk_mt_sgd(SMPK_MT_ARGS, int depth, float lr, float momentum, float dampening, float wd, int nesterov,
+                int first_run, int wd_after, float grad_scale, const int* noop);
+int smpk_mt_adagrad(SMPK_MT_ARGS, int depth, float lr, float eps, float wd, int decoupled, float grad_scale,
+                    const int* noop);
+int smpk_mt_lamb_stage1(SMPK_MT_ARGS, float beta1, float beta2, float eps, int step, int bias_correction, float wd,
+                        int grad_averaging, int adamw, const float* global_grad_norm, float max_grad_norm,
+                        float grad_scale, const int* noop);
+int smpk_mt_lamb_stage2(SMPK_MT_ARGS, int depth, float lr, float wd, int use_nvlamb, const float* p_norms,
+                        const float* u_norms, const int* noop);
+int smpk_mt_novograd(SMPK_MT_ARGS, int depth, float lr, float beta1, float beta2, float eps, int step,
+                     int bias_correction, float wd, int grad_averaging, int moment_mode, const float* v_norms,
+                     float grad_scale, const int* noop);
+int smpk_mt_l2norm_scratch_floats(void);
+int smpk_mt_l2norm(SMPK_MT_ARGS, float* out, float* per_tensor, float* scratch, int* flag, const int* noop);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SMPB200_KERNELS_H_ */

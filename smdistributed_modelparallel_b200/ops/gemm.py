@@ -1,0 +1,234 @@
+"""tcgen05 GEMM front-end and the autograd ``linear`` built on it.
+
+``gemm`` is the single entry to ``smpk_gemm`` (csrc/kernels/sm100/gemm_tcgen05.cu).  Operands are
+described by how they sit in memory, so forward / dgrad / wgrad of a linear layer and both batched
+attention GEMMs run on the same kernel without materialising transposes.
+
+Replaces ``F.linear`` / ``torch.matmul`` / ``torch.baddbmm`` on the reference's hot path (reference
+smdistributed/modelparallel/torch/nn/transformer.py:1107-1134,1476-1482,1515,1657,1810-1812) and the
+TorchScript bias-GELU (reference torch/nn/gelu.py:28-47), which is a GEMM epilogue here.
+"""
+
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from . import _native as N
+from .workspace import get_workspace
+
+EPI_NONE, EPI_GELU_TANH, EPI_GELU_ERF, EPI_DGELU_TANH, EPI_DGELU_ERF = range(5)
+_EPI_BY_NAME = {"none": EPI_NONE, "gelu_tanh": EPI_GELU_TANH, "gelu_erf": EPI_GELU_ERF,
+                "dgelu_tanh": EPI_DGELU_TANH, "dgelu_erf": EPI_DGELU_ERF}
+
+# diagnostics: how many GEMMs ran natively / fell back to torch.matmul (shape or alignment limits)
+stats = {"native": 0, "fallback": 0}
+
+# optional cap on the persistent grid (leaves SMs free for kernels on side streams)
+_max_ctas = 0
+
+
+def set_max_ctas(n: int) -> None:
+    global _max_ctas
+    _max_ctas = int(n)
+
+
+def _gelu_ref(x, kind):
+    return F.gelu(x, approximate="tanh" if kind == "tanh" else "none")
+
+
+def _dgelu_ref(x, kind):
+    x = x.detach().float().requires_grad_(True)
+    with torch.enable_grad():
+        y = _gelu_ref(x, kind)
+        (g,) = torch.autograd.grad(y.sum(), x)
+    return g
+
+
+def _reference(a, b, a_mn_major, b_mn_major, out_dtype, bias, residual, alpha, beta, epi, aux):
+    """fp32 restatement used for CPU tensors and unsupported layouts."""
+    A = a.float().transpose(-1, -2) if a_mn_major else a.float()
+    B = b.float().transpose(-1, -2) if b_mn_major else b.float()
+    v = torch.matmul(A, B.transpose(-1, -2)) * alpha
+    if bias is not None:
+        v = v + bias.float()
+    if epi in (EPI_DGELU_TANH, EPI_DGELU_ERF):
+        v = v * _dgelu_ref(residual, "tanh" if epi == EPI_DGELU_TANH else "erf")
+    elif residual is not None:
+        v = v + beta * residual.float()
+    if epi in (EPI_GELU_TANH, EPI_GELU_ERF):
+        if aux is not None:
+            aux.copy_(v.to(aux.dtype))
+        v = _gelu_ref(v, "tanh" if epi == EPI_GELU_TANH else "erf")
+    return v.to(out_dtype)
+
+
+def _native_ok(a, b, out, residual, bias):
+    if not a.is_cuda:
+        return False
+    if a.dtype not in (torch.bfloat16, torch.float16) or b.dtype != a.dtype:
+        return False
+    for t in (a, b):
+        if t.stride(-1) != 1 or t.stride(-2) % 8 or t.data_ptr() % 16:
+            return False
+        if t.dim() == 3 and t.stride(0) % 8:
+            return False
+    for t in (out, residual):
+        if t is not None and t.stride(-1) != 1:
+            return False
+    if bias is not None and not bias.is_contiguous():
+        return False
+    return True
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
+         out: torch.Tensor | None = None, out_dtype: torch.dtype | None = None, bias: torch.Tensor | None = None,
+         residual: torch.Tensor | None = None, alpha: float = 1.0, beta: float = 1.0, epilogue: str | int = "none",
+         aux_out: torch.Tensor | None = None) -> torch.Tensor:
+    """``out = epilogue(alpha * A @ B^T)`` with A logical [M,K] and B logical [N,K] (optionally batched).
+
+    ``a`` is stored ``[..., M, K]`` (K-major) or, with ``a_mn_major``, ``[..., K, M]``; likewise ``b``
+    is ``[..., N, K]`` or ``[..., K, N]``.  2-D or 3-D (leading batch) tensors; the last dimension
+    must be contiguous.  ``residual`` is added scaled by ``beta`` (it may be ``out`` itself for in-place
+    accumulation) or, for the ``dgelu_*`` epilogues, is the saved pre-activation.
+    """
+    epi = _EPI_BY_NAME[epilogue] if isinstance(epilogue, str) else int(epilogue)
+    assert a.dim() == b.dim() and a.dim() in (2, 3), "gemm expects 2-D or batched 3-D operands"
+    batch = a.shape[0] if a.dim() == 3 else 1
+    if a_mn_major:
+        K, M = a.shape[-2], a.shape[-1]
+    else:
+        M, K = a.shape[-2], a.shape[-1]
+    if b_mn_major:
+        Kb, Nn = b.shape[-2], b.shape[-1]
+    else:
+        Nn, Kb = b.shape[-2], b.shape[-1]
+    assert K == Kb, f"reduction mismatch: {tuple(a.shape)} vs {tuple(b.shape)}"
+    if out_dtype is None:
+        out_dtype = out.dtype if out is not None else a.dtype
+    out_shape = (batch, M, Nn) if a.dim() == 3 else (M, Nn)
+
+    if not _native_ok(a, b, out, residual, bias):
+        if a.is_cuda:
+            stats["fallback"] += 1
+        res = _reference(a, b, a_mn_major, b_mn_major, out_dtype, bias, residual, alpha, beta, epi, aux_out)
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res
+
+    if out is None:
+        out = torch.empty(out_shape, dtype=out_dtype, device=a.device)
+    assert tuple(out.shape) == out_shape and out.dtype == out_dtype
+    if aux_out is not None:
+        assert aux_out.shape == out.shape and aux_out.dtype == out.dtype and aux_out.stride() == out.stride()
+
+    def bs(t):
+        return t.stride(0) if t.dim() == 3 else 0
+
+    stats["native"] += 1
+    N.count_launch()
+    N.call(
+        "smpk_gemm", N.stream_ptr(a.device), N.dtype_code(a.dtype), N.dtype_code(out_dtype), M, Nn, K, batch,
+        a.data_ptr(), a.stride(-2), bs(a), int(a_mn_major),
+        b.data_ptr(), b.stride(-2), bs(b), int(b_mn_major),
+        out.data_ptr(), out.stride(-2), bs(out),
+        N.ptr(bias), N.dtype_code(bias.dtype) if bias is not None else 0,
+        N.ptr(residual), residual.stride(-2) if residual is not None else 0,
+        bs(residual) if residual is not None else 0,
+        N.dtype_code(residual.dtype) if residual is not None else 0,
+        N.ptr(aux_out), float(alpha), float(beta), epi, _max_ctas,
+    )
+    return out
+
+
+def colsum(x2d: torch.Tensor, out: torch.Tensor | None = None, accumulate: bool = False,
+           out_dtype: torch.dtype | None = None) -> torch.Tensor:
+    """Column sums of a [rows, N] matrix (bias gradients)."""
+    rows, n = x2d.shape
+    if out is None:
+        out = torch.empty(n, dtype=out_dtype or x2d.dtype, device=x2d.device)
+        accumulate = False
+    if not x2d.is_cuda or x2d.stride(-1) != 1 or x2d.dtype not in N._DTYPE_CODE:
+        s = x2d.float().sum(0)
+        out.copy_((out.float() + s) if accumulate else s)
+        return out
+    scratch = get_workspace(x2d.device, "colsum", N.query("smpk_colsum_scratch_floats", n) * 4)
+    N.count_launch(2)
+    N.call("smpk_colsum", N.stream_ptr(x2d.device), x2d.data_ptr(), N.dtype_code(x2d.dtype), rows, n, x2d.stride(0),
+           out.data_ptr(), N.dtype_code(out.dtype), int(accumulate), scratch.data_ptr())
+    return out
+
+
+class _LinearFn(torch.autograd.Function):
+    """y = x W^T (+ b) with optional fused GELU; backward runs dgrad / wgrad on the same kernel.
+
+    When the weight carries a ``main_grad`` fp32 buffer (set by the bucketed reducer / sharded
+    optimizer) wgrad accumulates straight into it from the GEMM epilogue.
+    """
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, activation):
+        ctx.activation = activation
+        x2 = x.reshape(-1, x.shape[-1])
+        if activation is None:
+            y = gemm(x2, weight, bias=bias)
+            pre = None
+        else:
+            need_pre = any(ctx.needs_input_grad[:3])
+            y = torch.empty(x2.shape[0], weight.shape[0], dtype=x.dtype, device=x.device)
+            pre = torch.empty_like(y) if need_pre else None
+            gemm(x2, weight, bias=bias, out=y, epilogue=f"gelu_{activation}", aux_out=pre)
+        ctx.save_for_backward(x2, weight, pre)
+        ctx.has_bias = bias is not None
+        ctx.x_shape = x.shape
+        return y.reshape(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, pre = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        if ctx.activation is not None:
+            # dz = dy * gelu'(z): one elementwise pass shared by dgrad, wgrad and the bias grad
+            from .gelu import gelu_backward
+            dy2 = gelu_backward(dy2, pre, ctx.activation)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dy2, weight, b_mn_major=True).reshape(ctx.x_shape)
+        if ctx.needs_input_grad[1]:
+            mg = getattr(weight, "main_grad", None)
+            if mg is not None:
+                gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=mg, residual=mg, beta=1.0)
+                dw = None
+                if getattr(weight, "grad_added_to_main_grad", None) is not None:
+                    weight.grad_added_to_main_grad = True
+            else:
+                dw = gemm(dy2, x2, a_mn_major=True, b_mn_major=True)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = colsum(dy2)
+        return dx, dw, db, None
+
+
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = None,
+           activation: str | None = None) -> torch.Tensor:
+    """``x @ weight.T + bias`` followed by an optional fused GELU (``"tanh"`` or ``"erf"``)."""
+    if bias is not None and bias.dtype != x.dtype and not x.is_cuda:
+        bias = bias.to(x.dtype)
+    return _LinearFn.apply(x, weight, bias, activation)
+
+
+def bmm_nt(a: torch.Tensor, b: torch.Tensor, alpha: float = 1.0, out_dtype=None) -> torch.Tensor:
+    """Batched ``a @ b^T``: a [B,M,K], b [B,N,K] -> [B,M,N] (attention scores)."""
+    return gemm(a, b, alpha=alpha, out_dtype=out_dtype)
+
+
+def bmm_nn(a: torch.Tensor, b: torch.Tensor, alpha: float = 1.0, out_dtype=None) -> torch.Tensor:
+    """Batched ``a @ b``: a [B,M,K], b [B,K,N] -> [B,M,N] (probabilities x values)."""
+    return gemm(a, b, b_mn_major=True, alpha=alpha, out_dtype=out_dtype)
+
+
+def bmm_tn(a: torch.Tensor, b: torch.Tensor, alpha: float = 1.0, out_dtype=None) -> torch.Tensor:
+    """Batched ``a^T @ b``: a [B,K,M], b [B,K,N] -> [B,M,N] (attention weight-gradient shapes)."""
+    return gemm(a, b, a_mn_major=True, b_mn_major=True, alpha=alpha, out_dtype=out_dtype)

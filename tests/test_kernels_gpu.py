@@ -1,0 +1,302 @@
+"""Numerics of every sm_100a kernel against a plain fp32 PyTorch restatement (1 GPU).
+
+Mirrors the reference's kernel tier (reference smdistributed/modelparallel/test/torch/test_kernels.py:14-86:
+fused softmax vs F.softmax at [4,16,1024,1024], atol 1e-3) and extends it to every native op.
+"""
+
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _rel_err(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+def _report(name, got, ref, tol):
+    err = _rel_err(got, ref)
+    mx = (got.float() - ref.float()).abs().max().item()
+    assert err < tol, f"{name}: rel-l2 {err:.3e} max-abs {mx:.3e} (tol {tol:.1e}) shape {tuple(ref.shape)}"
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _lib():
+    from smdistributed_modelparallel_b200.ops import _native
+
+    _native.load()
+    assert _native.query("smpk_device_cc") >= 100, "tests need an sm_100 device"
+
+
+GEMM_SHAPES = [
+    (128, 256, 64), (128, 256, 256), (256, 512, 1024), (384, 768, 320), (100, 200, 72), (1000, 136, 520),
+    (4096, 4096, 4096), (64, 64, 64), (130, 72, 64), (2048, 50304 // 8, 768),
+]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+@pytest.mark.parametrize("layout", ["nt", "nn", "tn"])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_gemm_layouts(M, N, K, layout, dtype):
+    from smdistributed_modelparallel_b200.ops.gemm import gemm, stats
+
+    if dtype == torch.float16 and M > 1024:
+        pytest.skip("fp16 covered on the small shapes")
+    torch.manual_seed(M * 7 + N * 3 + K)
+    A = torch.randn(M, K, device=DEV, dtype=dtype)
+    B = torch.randn(N, K, device=DEV, dtype=dtype)
+    ref = A.float() @ B.float().t()
+    before = dict(stats)
+    if layout == "nt":
+        out = gemm(A, B)
+    elif layout == "nn":
+        out = gemm(A, B.t().contiguous(), b_mn_major=True)
+    else:
+        out = gemm(A.t().contiguous(), B.t().contiguous(), a_mn_major=True, b_mn_major=True)
+    torch.cuda.synchronize()
+    aligned = all(s % 8 == 0 for s in (M, N, K))
+    if aligned:
+        assert stats["native"] == before["native"] + 1, "aligned shape must take the tcgen05 kernel"
+    _report(f"gemm {layout}", out, ref, 1e-2)
+
+
+@pytest.mark.parametrize("epi", ["none", "gelu_tanh", "gelu_erf"])
+def test_gemm_epilogues(epi):
+    from smdistributed_modelparallel_b200.ops.gemm import gemm
+
+    torch.manual_seed(1)
+    M, N, K = 512, 1024, 256
+    A = torch.randn(M, K, device=DEV, dtype=torch.bfloat16) * 0.5
+    B = torch.randn(N, K, device=DEV, dtype=torch.bfloat16) * 0.1
+    bias = torch.randn(N, device=DEV, dtype=torch.bfloat16)
+    R = torch.randn(M, N, device=DEV, dtype=torch.bfloat16)
+    pre = A.float() @ B.float().t() * 0.5 + bias.float()
+    if epi == "none":
+        out = gemm(A, B, bias=bias, residual=R, alpha=0.5, beta=2.0)
+        _report("gemm bias+residual", out, pre + 2.0 * R.float(), 1e-2)
+        acc = torch.randn(M, N, device=DEV, dtype=torch.float32)
+        ref = acc + A.float() @ B.float().t()
+        gemm(A, B, out=acc, residual=acc, beta=1.0)
+        _report("gemm fp32 accumulate", acc, ref, 1e-2)
+    else:
+        aux = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+        out = gemm(A, B, bias=bias, alpha=0.5, epilogue=epi, aux_out=aux)
+        _report("gemm aux", aux, pre, 1e-2)
+        _report("gemm gelu", out, F.gelu(pre, approximate="tanh" if epi == "gelu_tanh" else "none"), 1e-2)
+        z = torch.randn(M, N, device=DEV, dtype=torch.bfloat16)
+        dz = gemm(A, B, residual=z, epilogue="d" + epi)
+        zz = z.float().requires_grad_(True)
+        (g,) = torch.autograd.grad(F.gelu(zz, approximate="tanh" if epi == "gelu_tanh" else "none").sum(), zz)
+        _report("gemm dgelu", dz, (A.float() @ B.float().t()) * g, 1e-2)
+
+
+def test_gemm_batched_strided():
+    from smdistributed_modelparallel_b200.ops.gemm import gemm
+
+    torch.manual_seed(2)
+    Bn, S, d = 6, 384, 128
+    q = torch.randn(Bn, S, d, device=DEV, dtype=torch.bfloat16)
+    k = torch.randn(Bn, S, d, device=DEV, dtype=torch.bfloat16)
+    v = torch.randn(Bn, S, d, device=DEV, dtype=torch.bfloat16)
+    s = gemm(q, k, alpha=0.125)
+    _report("bmm nt", s, torch.bmm(q.float(), k.float().transpose(1, 2)) * 0.125, 1e-2)
+    p = torch.softmax(s.float(), -1).to(torch.bfloat16)
+    o = gemm(p, v, b_mn_major=True)
+    _report("bmm nn", o, torch.bmm(p.float(), v.float()), 1e-2)
+    dv = gemm(p, o, a_mn_major=True, b_mn_major=True)
+    _report("bmm tn", dv, torch.bmm(p.float().transpose(1, 2), o.float()), 1e-2)
+
+
+def test_linear_autograd_matches_torch():
+    from smdistributed_modelparallel_b200.ops.gemm import linear
+
+    torch.manual_seed(3)
+    x = torch.randn(4, 96, 512, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    w = (torch.randn(1024, 512, device=DEV, dtype=torch.bfloat16) * 0.05).requires_grad_(True)
+    b = torch.randn(1024, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    for act in (None, "tanh"):
+        y = linear(x, w, b, act)
+        go = torch.randn_like(y)
+        gx, gw, gb = torch.autograd.grad(y, (x, w, b), go)
+        xf, wf, bf = (t.detach().float().requires_grad_(True) for t in (x, w, b))
+        yr = F.linear(xf, wf, bf)
+        if act:
+            yr = F.gelu(yr, approximate="tanh")
+        rx, rw, rb = torch.autograd.grad(yr, (xf, wf, bf), go.float())
+        _report("linear y", y, yr, 1e-2)
+        _report("linear dx", gx, rx, 2e-2)
+        _report("linear dw", gw, rw, 2e-2)
+        _report("linear db", gb, rb, 2e-2)
+
+
+@pytest.mark.parametrize("H", [768, 1024, 4096, 6144, 845])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_layernorm(H, dtype):
+    from smdistributed_modelparallel_b200.ops.layernorm import layer_norm
+
+    torch.manual_seed(4)
+    rows = 1031
+    x = torch.randn(rows, H, device=DEV, dtype=dtype, requires_grad=True)
+    r = torch.randn(rows, H, device=DEV, dtype=dtype, requires_grad=True)
+    g = torch.randn(H, device=DEV, dtype=dtype, requires_grad=True)
+    b = torch.randn(H, device=DEV, dtype=dtype, requires_grad=True)
+    tol = 1e-2 if dtype == torch.bfloat16 else 1e-4
+    y = layer_norm(x, g, b, 1e-5)
+    go = torch.randn_like(y)
+    gx, gg, gb = torch.autograd.grad(y, (x, g, b), go)
+    xf, gf, bf = (t.detach().float().requires_grad_(True) for t in (x, g, b))
+    yr = F.layer_norm(xf, (H,), gf, bf, 1e-5)
+    rx, rg, rb = torch.autograd.grad(yr, (xf, gf, bf), go.float())
+    _report("ln y", y, yr, tol)
+    _report("ln dx", gx, rx, tol)
+    _report("ln dgamma", gg, rg, 2 * tol)
+    _report("ln dbeta", gb, rb, 2 * tol)
+    # fused residual
+    y2, s2 = layer_norm(x, g, b, 1e-5, residual=r)
+    gx2, gr2 = torch.autograd.grad((y2, s2), (x, r), (go, go))
+    xf, rf = (t.detach().float().requires_grad_(True) for t in (x, r))
+    sr = (xf + rf).to(dtype).float() if dtype != torch.float32 else xf + rf
+    sr2 = xf + rf
+    yr2 = F.layer_norm(sr2, (H,), g.detach().float(), b.detach().float(), 1e-5)
+    rx2, rr2 = torch.autograd.grad((yr2, sr2), (xf, rf), (go.float(), go.float()))
+    _report("ln+res y", y2, yr2, tol)
+    _report("ln+res sum", s2, sr, tol)
+    _report("ln+res dx", gx2, rx2, tol)
+    _report("ln+res dres", gr2, rr2, tol)
+
+
+def test_softmax_reference_shape():
+    """The reference's own test shape: [4,16,1024,1024] fp16, atol 1e-3."""
+    from smdistributed_modelparallel_b200.ops.softmax import scaled_masked_softmax, scaled_upper_triang_masked_softmax
+
+    torch.manual_seed(5)
+    x = torch.randn(4, 16, 1024, 1024, device=DEV, dtype=torch.float16)
+    mask = torch.rand(4, 1, 1024, 1024, device=DEV) > 0.7
+    scale = 0.37
+    y = scaled_masked_softmax(x, mask, scale)
+    ref = torch.softmax((x.float() * scale).masked_fill(mask, float("-inf")), -1)
+    assert (y.float() - ref).abs().max().item() < 1e-3
+    x3 = x.reshape(64, 1024, 1024)
+    y3 = scaled_upper_triang_masked_softmax(x3, scale)
+    tri = torch.ones(1024, 1024, device=DEV, dtype=torch.bool).tril()
+    ref3 = torch.softmax((x3.float() * scale).masked_fill(~tri, float("-inf")), -1)
+    assert (y3.float() - ref3).abs().max().item() < 1e-3
+
+
+@pytest.mark.parametrize("Sk", [64, 2048, 4096, 200])
+def test_softmax_backward(Sk):
+    from smdistributed_modelparallel_b200.ops.softmax import scaled_upper_triang_masked_softmax
+
+    torch.manual_seed(6)
+    Sq = Sk
+    x = torch.randn(3, Sq, Sk, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    y = scaled_upper_triang_masked_softmax(x, 0.5)
+    go = torch.randn_like(y)
+    (gx,) = torch.autograd.grad(y, x, go)
+    xf = x.detach().float().requires_grad_(True)
+    tri = torch.ones(Sq, Sk, device=DEV, dtype=torch.bool).tril()
+    yr = torch.softmax((xf * 0.5).masked_fill(~tri, float("-inf")), -1)
+    (rx,) = torch.autograd.grad(yr, xf, go.float())
+    _report("softmax y", y, yr, 1e-2)
+    _report("softmax dx", gx, rx, 2e-2)
+
+
+@pytest.mark.parametrize("V", [50304, 32000 // 4, 1001])
+def test_cross_entropy(V):
+    from smdistributed_modelparallel_b200.ops.cross_entropy import cross_entropy
+
+    torch.manual_seed(7)
+    rows = 777
+    lg = (torch.randn(rows, V, device=DEV, dtype=torch.bfloat16) * 3).requires_grad_(True)
+    t = torch.randint(0, V, (rows,), device=DEV)
+    t[5] = -100
+    loss = cross_entropy(lg, t)
+    (g,) = torch.autograd.grad(loss, lg)
+    lf = lg.detach().float().requires_grad_(True)
+    lr = F.cross_entropy(lf, t)
+    (gr,) = torch.autograd.grad(lr, lf)
+    assert abs(loss.item() - lr.item()) < 2e-3 * max(1.0, abs(lr.item()))
+    _report("ce grad", g, gr, 2e-2)
+
+
+def test_bias_gelu_and_colsum():
+    from smdistributed_modelparallel_b200.ops.gelu import bias_gelu
+    from smdistributed_modelparallel_b200.ops.gemm import colsum
+
+    torch.manual_seed(8)
+    x = torch.randn(513, 3072, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    b = torch.randn(3072, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    for mode in ("tanh", "erf"):
+        y = bias_gelu(x, b, mode)
+        go = torch.randn_like(y)
+        gx, gb = torch.autograd.grad(y, (x, b), go)
+        xf, bf = (t.detach().float().requires_grad_(True) for t in (x, b))
+        yr = F.gelu(xf + bf, approximate="tanh" if mode == "tanh" else "none")
+        rx, rb = torch.autograd.grad(yr, (xf, bf), go.float())
+        _report("bias_gelu y", y, yr, 1e-2)
+        _report("bias_gelu dx", gx, rx, 1e-2)
+        _report("bias_gelu db", gb, rb, 2e-2)
+    m = torch.randn(1000, 1001, device=DEV, dtype=torch.float32)
+    _report("colsum scalar path", colsum(m), m.sum(0), 1e-5)
+
+
+@pytest.mark.parametrize("style,rot", [(1, 64), (2, 32), (0, 0)])
+def test_qkv_rotary_and_attention(style, rot):
+    from smdistributed_modelparallel_b200.ops import attention as A
+
+    torch.manual_seed(9)
+    B, S, h, d = 2, 256, 4, 128
+    fused = (torch.randn(B * S, 3 * h * d, device=DEV, dtype=torch.bfloat16) * 0.5).requires_grad_(True)
+    cos, sin = A.rotary_tables(S, max(rot, 2), 10000.0, DEV)
+    q, k, v = A.qkv_split_rotary(fused, B, S, h, d, rot, style, cos, sin, 0)
+    o = A.heads_to_tokens(A.core_attention(q, k, v, causal=True))
+    go = torch.randn_like(o)
+    (gf,) = torch.autograd.grad(o, fused, go)
+    # fp32 oracle on the CPU reference path of the same functions
+    ff = fused.detach().float().cpu().requires_grad_(True)
+    qr, kr, vr = A.qkv_split_rotary(ff, B, S, h, d, rot, style, cos.cpu(), sin.cpu(), 0)
+    orf = F.scaled_dot_product_attention(qr, kr, vr, is_causal=True).transpose(1, 2).reshape(B, S, h * d)
+    (gr,) = torch.autograd.grad(orf, ff, go.float().cpu())
+    _report("attention out", o.cpu(), orf, 2e-2)
+    _report("attention dfused", gf.cpu(), gr, 3e-2)
+
+
+def test_multi_tensor_ops():
+    from smdistributed_modelparallel_b200.ops import multi_tensor as MT
+
+    torch.manual_seed(10)
+    sizes = [1, 7, 4096, 65536 + 3, 300001]
+    g = [torch.randn(s, device=DEV, dtype=torch.bfloat16) for s in sizes]
+    p = [torch.randn(s, device=DEV, dtype=torch.float32) for s in sizes]
+    m = [torch.zeros(s, device=DEV) for s in sizes]
+    v = [torch.zeros(s, device=DEV) for s in sizes]
+    lp = [torch.empty(s, device=DEV, dtype=torch.bfloat16) for s in sizes]
+    ref_p = [t.clone() for t in p]
+    opt = torch.optim.AdamW([torch.nn.Parameter(t) for t in ref_p], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    flag = torch.zeros(1, dtype=torch.int32, device=DEV)
+    for step in (1, 2, 3):
+        for q_, gg in zip(opt.param_groups[0]["params"], g):
+            q_.grad = gg.float() * 0.5
+        opt.step()
+        MT.multi_tensor_applier(MT.multi_tensor_adam, flag, [g, p, m, v, lp], 1e-2, 0.9, 0.95, 1e-8, step, 1, True, 0.1, 0.5)
+    for a, b_, l in zip(p, opt.param_groups[0]["params"], lp):
+        _report("adam p", a, b_.detach(), 1e-5)
+        _report("adam lowprec", l, b_.detach(), 1e-2)
+    norm, per = MT.multi_tensor_l2norm(65536, flag, [g], True)
+    ref = torch.sqrt(sum(t.float().pow(2).sum() for t in g))
+    assert abs(norm.item() - ref.item()) < 1e-3 * ref.item()
+    _report("per-tensor norm", per, torch.stack([t.float().norm() for t in g]), 1e-4)
+    out = [torch.empty_like(t, dtype=torch.float32) for t in g]
+    MT.multi_tensor_scale(65536, flag, [g, out], 0.25)
+    for a, b_ in zip(out, g):
+        _report("scale", a, b_.float() * 0.25, 1e-6)
+    assert flag.item() == 0
+    g[2][5] = float("inf")
+    MT.multi_tensor_scale(65536, flag, [g, out], 0.25)
+    assert flag.item() == 1
