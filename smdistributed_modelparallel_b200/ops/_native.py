@@ -42,7 +42,7 @@ P = c_void_p
 I = c_int
 L = c_longlong
 F = c_float
-_MT = [P, I, POINTER(P), POINTER(L), POINTER(I), I]
+_MT = [P, I, P, P, P, I]  # stream, n, void*** lists, long long* sizes, int* dtypes, chunk
 
 _SIGNATURES = {
     "smpk_version": ([], I),

@@ -36,7 +36,9 @@ def _pack(tensor_lists):
     for lst in tensor_lists:
         for t, ref in zip(lst, tensor_lists[0]):
             assert t.numel() == ref.numel() and t.is_contiguous() and t.dtype == lst[0].dtype
-    return n, lists, sizes, dtypes, arrs
+    keep = (arrs, lists, sizes, dtypes)
+    as_ptr = lambda a: ctypes.cast(a, ctypes.c_void_p)
+    return n, as_ptr(lists), as_ptr(sizes), as_ptr(dtypes), keep
 
 
 def _is_cuda(tensor_lists):
