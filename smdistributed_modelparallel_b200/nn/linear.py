@@ -1,0 +1,51 @@
+"""``DistributedLinear``: nn.Linear with the input features split across the tensor-parallel group.
+
+Reference: smdistributed/modelparallel/torch/nn/linear.py:12-63 - all-to-all (batch <-> features),
+local GEMM, reduce-scatter over the batch.  Each rank passes its own batch slice and
+receives the output for that slice; the GEMM runs on the tcgen05 kernel.
+"""
+
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn as nn
+
+from ..parallel import tp_ops
+from .dist_module import DistributedModule
+from .utils import (get_local_channels, get_split_shapes, initialize_with_input_partition, parameter_creation_scope,
+                    reduce_scatter_for_tp, scatter_and_merge_for_tp, tp_group, tp_rank, tp_size)
+
+
+class DistributedLinear(DistributedModule):
+    def __init__(self, in_features, out_features, bias=True, dtype=None, device=None):
+        super().__init__()
+        self.in_features, self.out_features = in_features, out_features
+        self.local_in_features = get_local_channels(in_features)
+        with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):
+            with initialize_with_input_partition(self, exclude_from_dist=["bias"]):
+                self.weight = nn.Parameter(torch.empty(out_features, self.local_in_features, device=device))
+                self.bias = nn.Parameter(torch.zeros(out_features, device=device)) if (bias and tp_rank() == 0) else None
+                nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+                if self.bias is not None:
+                    bound = 1.0 / math.sqrt(in_features)
+                    nn.init.uniform_(self.bias, -bound, bound)
+        self.weight_split_shapes = get_split_shapes(in_features)
+
+    def forward(self, x):
+        t = tp_size()
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, x.shape[-1])
+        if t == 1:
+            y = tp_ops.row_parallel_linear(x2, self.weight, self.bias, None, scatter_output=False)
+            return y.reshape(*lead, self.out_features)
+        # [b, K] on each rank -> [B, K/t]: split features, merge batch
+        xs = scatter_and_merge_for_tp(x2, split_dim=1, merge_dim=0, split_shapes=self.weight_split_shapes)
+        y = tp_ops.row_parallel_linear(xs.contiguous(), self.weight, self.bias, None, scatter_output=False)
+        rows = x2.shape[0]
+        if all(s == rows for s in [rows]) and y.shape[0] == rows * t:
+            y = tp_ops.ScatterSumTokens.apply(y, tp_group())
+        else:
+            y = reduce_scatter_for_tp(y, 0)
+        return y.reshape(*lead, self.out_features)

@@ -1,0 +1,209 @@
+"""Activation checkpointing: ``smp.checkpoint``, ``smp.checkpoint_sequential`` and the machinery behind
+``smp.set_activation_checkpointing``.
+
+Reference: smdistributed/modelparallel/torch/patches/checkpoint.py:108-359 (``CheckpointTupledFunction``
+handling arbitrary argument structures, RNG + tensor-parallel seed restoration; ``checkpoint`` :312-324;
+``checkpoint_sequential`` :327-359) and torch/sequential.py:187-264 (strategies ``each`` /
+``contiguous`` / ``group_N`` over an ``nn.Sequential``).  When ``offload_activations`` is on, the saved
+inputs of each checkpoint go to pinned host memory through the side-stream offloader (``offload.py``).
+"""
+
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from ..backend.exceptions import CheckpointingConfigError, InvalidReturnTypeFromCheckpointedModuleError
+from ..backend.split import map_structure
+
+
+def _flatten(obj, tensors):
+    """Replace tensors by placeholders, collecting them in ``tensors``."""
+    def f(x):
+        if torch.is_tensor(x):
+            tensors.append(x)
+            return _Slot(len(tensors) - 1)
+        return x
+    return map_structure(f, obj)
+
+
+def _unflatten(skel, tensors):
+    return map_structure(lambda x: tensors[x.i] if isinstance(x, _Slot) else x, skel)
+
+
+class _Slot:
+    __slots__ = ("i",)
+
+    def __init__(self, i):
+        self.i = i
+
+
+def _rng_snapshot():
+    from ..state_mod import state
+
+    snap = {"cpu": torch.get_rng_state()}
+    if torch.cuda.is_available():
+        snap["cuda"] = torch.cuda.get_rng_state()
+    if getattr(state, "initialized", False):
+        snap["smp"] = dict(state.rng_manager.get_states())
+    return snap
+
+
+def _rng_restore(snap):
+    from ..state_mod import state
+
+    torch.set_rng_state(snap["cpu"])
+    if "cuda" in snap:
+        torch.cuda.set_rng_state(snap["cuda"])
+    if "smp" in snap:
+        state.rng_manager.set_states(snap["smp"])
+
+
+class CheckpointFunction(torch.autograd.Function):
+    """Run ``fn(*args, **kwargs)`` without storing intermediate activations; recompute in backward."""
+
+    @staticmethod
+    def forward(ctx, fn, preserve_rng_state, skel, holder, *tensors):
+        from ..state_mod import state
+
+        ctx.fn, ctx.skel, ctx.preserve = fn, skel, preserve_rng_state
+        ctx.rng = _rng_snapshot() if preserve_rng_state else None
+        ctx.autocast = torch.is_autocast_enabled()
+        args, kwargs = _unflatten(skel, list(tensors))
+        with torch.no_grad():
+            out = fn(*args, **kwargs)
+        # what to keep for the recomputation: the input tensors (possibly offloaded to pinned host memory)
+        offload = getattr(state, "initialized", False) and state.cfg.offload_activations and \
+            any(t.is_cuda for t in tensors)
+        ctx.requires = [t.requires_grad for t in tensors]
+        if offload:
+            from ..offload import get_offloader
+            off = get_offloader()
+            ctx.offload_handles = [off.offload(t) if (t.is_cuda and t.is_floating_point()) else t for t in tensors]
+            ctx.saved_direct = None
+        else:
+            ctx.offload_handles = None
+            ctx.save_for_backward(*tensors)
+        out_tensors = []
+        ctx.out_skel = _flatten(out, out_tensors)
+        if not out_tensors:
+            raise InvalidReturnTypeFromCheckpointedModuleError()
+        ctx.n_out = len(out_tensors)
+        holder["out_skel"] = ctx.out_skel
+        return tuple(out_tensors)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        if ctx.offload_handles is not None:
+            from ..offload import get_offloader
+            off = get_offloader()
+            saved = [off.load(h) if not torch.is_tensor(h) else h for h in ctx.offload_handles]
+        else:
+            saved = list(ctx.saved_tensors)
+        inputs = []
+        for t, req in zip(saved, ctx.requires):
+            d = t.detach()
+            d.requires_grad_(req and d.is_floating_point())
+            inputs.append(d)
+        args, kwargs = _unflatten(ctx.skel, inputs)
+        outer = _rng_snapshot() if ctx.preserve else None
+        if ctx.preserve:
+            _rng_restore(ctx.rng)
+        try:
+            with torch.enable_grad():
+                out = ctx.fn(*args, **kwargs)
+        finally:
+            if ctx.preserve:
+                _rng_restore(outer)
+        outs = []
+        _flatten(out, outs)
+        pairs = [(o, g) for o, g in zip(outs, grads) if o.requires_grad and g is not None]
+        if pairs:
+            torch.autograd.backward([o for o, _ in pairs], [g for _, g in pairs])
+        in_grads = [t.grad if (t.requires_grad) else None for t in inputs]
+        return (None, None, None, None, *in_grads)
+
+
+def checkpoint(module_or_fn, *args, preserve_rng_state: bool = True, **kwargs):
+    """Checkpoint one call of a module (or function): activations inside are recomputed in backward."""
+    tensors = []
+    skel = _flatten((args, kwargs), tensors)
+    if not any(t.requires_grad for t in tensors) and not any(
+            p.requires_grad for p in (module_or_fn.parameters() if isinstance(module_or_fn, nn.Module) else [])):
+        return module_or_fn(*args, **kwargs)
+    # autograd.Function only tracks tensor arguments that require grad; make sure at least one does so the
+    # recomputation is reached even when only parameters need gradients
+    anchor = None
+    if not any(t.requires_grad for t in tensors):
+        dev = tensors[0].device if tensors else None
+        anchor = torch.zeros((), requires_grad=True, device=dev)
+        tensors = tensors + [anchor]
+    fn = module_or_fn if anchor is None else _with_anchor(module_or_fn)
+    if anchor is not None:
+        skel = (skel[0] + (_Slot(len(tensors) - 1),), skel[1])
+    holder = {}
+    outs = CheckpointFunction.apply(fn, preserve_rng_state, skel, holder, *tensors)
+    return _unflatten(holder["out_skel"], list(outs))
+
+
+def _with_anchor(fn):
+    def wrapped(*args, **kwargs):
+        return fn(*args[:-1], **kwargs)
+    return wrapped
+
+
+def _chunks(n, strategy):
+    if strategy == "each":
+        return [(i, i + 1) for i in range(n)]
+    if strategy == "contiguous":
+        return [(0, n)]
+    if isinstance(strategy, str) and strategy.startswith("group_"):
+        g = int(strategy[6:])
+        if g <= 0:
+            raise CheckpointingConfigError("group size must be positive")
+        return [(i, min(n, i + g)) for i in range(0, n, g)]
+    raise CheckpointingConfigError(f"unknown checkpointing strategy {strategy!r}")
+
+
+def checkpoint_sequential(sequential, input, strategy="each", preserve_rng_state=True, pack_args_as_tuple=False):
+    """Checkpoint an ``nn.Sequential`` in groups of layers: ``each`` layer separately, all layers as one
+    ``contiguous`` block, or ``group_N`` layers at a time."""
+    if not isinstance(sequential, nn.Sequential):
+        raise CheckpointingConfigError("checkpoint_sequential expects an nn.Sequential")
+    layers = list(sequential.children())
+
+    def run(a, b):
+        def fn(x):
+            for layer in layers[a:b]:
+                x = layer(*x) if (isinstance(x, tuple) and not pack_args_as_tuple) else layer(x)
+            return x
+        return fn
+
+    x = input
+    for a, b in _chunks(len(layers), strategy):
+        x = checkpoint(run(a, b), x, preserve_rng_state=preserve_rng_state)
+    return x
+
+
+def apply_configured_checkpointing(root: nn.Module):
+    """Wrap ``forward`` of every module configured through ``smp.set_activation_checkpointing``."""
+    from ..state_mod import state
+
+    mm = state.module_manager
+    for m in root.modules():
+        cfg = mm.get_checkpoint_config(m)
+        if cfg is None or not cfg.enabled or getattr(m, "_smp_ckpt_wrapped", False):
+            continue
+        orig = m.forward
+        if isinstance(m, nn.Sequential):
+            def fwd(inp, _m=m, _cfg=cfg, _orig=orig):
+                if not torch.is_grad_enabled():
+                    return _orig(inp)
+                return checkpoint_sequential(_m, inp, _cfg.strategy, _cfg.preserve_rng_state, _cfg.pack_args_as_tuple)
+        else:
+            def fwd(*args, _cfg=cfg, _orig=orig, **kwargs):
+                if not torch.is_grad_enabled():
+                    return _orig(*args, **kwargs)
+                return checkpoint(_orig, *args, preserve_rng_state=_cfg.preserve_rng_state, **kwargs)
+        m.forward = fwd
+        m._smp_ckpt_wrapped = True
