@@ -1,0 +1,262 @@
+#!/usr/bin/env python
+"""Flagship training benchmark (driver contract: see README / DESIGN.md).
+
+    python bench.py --gpus 1 --steps 10 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+Metric: training tokens/s of GPT-J 6B (bf16, seq 2048, random-init weights, synthetic tokens) through the
+library's public API - smp.init / smp.DistributedModel / smp.DistributedOptimizer / @smp.step - one
+optimizer step per timed step.  Rank 0 prints ONE JSON line.
+
+  value      device-timed (CUDA events, max over ranks) with the token batch already resident on the GPU
+  e2e.value  the same step fed from pinned host memory (H2D copy of the ids every step) and read back
+             (D2H of the loss every step)
+
+`--impl reference` would run the unmodified reference; it cannot be installed here (binary-only wheel
+with its native libraries missing), so that arm reports `unavailable`.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "baseline"])
+    ap.add_argument("--model", default=os.environ.get("BENCH_MODEL", "gpt-j-6b"))
+    ap.add_argument("--seq", type=int, default=0)
+    ap.add_argument("--micro-batch", type=int, default=0, help="sequences per microbatch per data-parallel rank")
+    ap.add_argument("--microbatches", type=int, default=0)
+    ap.add_argument("--parallelism", default="", help="e.g. tp2, pp2, pp2tp4, sdp8, dp2 (default: chosen per N)")
+    ap.add_argument("--checkpoint", type=int, default=-1, help="activation checkpointing (1/0, default auto)")
+    ap.add_argument("--layers", type=int, default=0, help="debug only: override layer count (marks the run invalid)")
+    return ap.parse_args()
+
+
+def reference_arm(args):
+    why = ("reference is an unpacked cp38 binary wheel with no setup.py/pyproject and all five native libraries "
+           "(smplib.so, smp_torch_cuda_lib.so, amp_C.so, ...) absent; pip install of /root/reference fails: not installable")
+    print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                mx = float(parts[2])
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def pick_parallelism(n, spec):
+    """Returns (pp, tp, sdp, label)."""
+    import re
+
+    if not spec:
+        spec = {1: "dp1", 2: "tp2", 4: "tp4", 8: "pp2tp4"}.get(n, f"tp{n}")
+    pp = int(m.group(1)) if (m := re.search(r"pp(\d+)", spec)) else 1
+    tp = int(m.group(1)) if (m := re.search(r"tp(\d+)", spec)) else 1
+    sdp = int(m.group(1)) if (m := re.search(r"sdp(\d+)", spec)) else 1
+    return pp, tp, sdp, spec
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200.models.configs import MODEL_CONFIGS, param_count, train_flops_per_token
+    from smdistributed_modelparallel_b200.ops import _native as N
+
+    n = int(os.environ.get("WORLD_SIZE", "1"))
+    if n != args.gpus:
+        print(f"[bench] WORLD_SIZE={n} but --gpus {args.gpus}; using WORLD_SIZE", file=sys.stderr)
+    pp, tp, sdp, label = pick_parallelism(n, args.parallelism)
+    dp = n // (pp * tp)
+    mcfg = dict(MODEL_CONFIGS[args.model])
+    if args.layers:
+        mcfg["num_layers"] = args.layers
+    seq = args.seq or mcfg["num_positions"]
+    # per-N batch geometry (weak scaling: sequences per step grow with N)
+    micro = args.micro_batch or 4
+    nmb = args.microbatches or (2 if pp == 1 else 8)
+    baseline = args.impl == "baseline"
+
+    conf = {"microbatches": nmb, "bf16": True, "pipeline_parallel_degree": pp, "tensor_parallel_degree": tp,
+            "ddp": n > 1, "delayed_parameter_initialization": True, "pipeline": "interleaved"}
+    if sdp > 1:
+        conf["sharded_data_parallel_degree"] = sdp
+    if tp > 1:
+        conf["prescaled_batch"] = False
+    os.environ.setdefault("SMP_LOG_LEVEL", "warning")
+    smp.init(conf)
+    if baseline:
+        from smdistributed_modelparallel_b200 import baseline_mode
+        baseline_mode.enable()
+    dev = torch.device("cuda", smp.local_rank())
+    torch.manual_seed(1234 + smp.rank())
+
+    with smp.model_creation(tensor_parallelism=tp > 1, dtype=torch.bfloat16):
+        module = smp.nn.DistributedTransformerLMHead(**mcfg)
+    use_ckpt = args.checkpoint if args.checkpoint >= 0 else 0
+    if use_ckpt:
+        smp.set_activation_checkpointing(module.transformer.seq_layers, pack_args_as_tuple=True, strategy="each")
+    model = smp.DistributedModel(module)
+    optimizer = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-4, betas=(0.9, 0.95),
+                                                           weight_decay=0.1))
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    # batch seen by one rank per step; tp ranks each bring their own sequences (non-prescaled batch)
+    per_rank_batch = micro * nmb
+    global_batch = per_rank_batch * (dp * tp)
+    tokens_per_step = global_batch * seq
+    vocab = mcfg["vocab_size"]
+    host_ids = [torch.randint(0, vocab, (per_rank_batch, seq), dtype=torch.int64).pin_memory() for _ in range(4)]
+    dev_ids = torch.randint(0, vocab, (per_rank_batch, seq), dtype=torch.int64, device=dev)
+
+    def one_step(ids):
+        optimizer.zero_grad()
+        out = train_step(model, ids)
+        optimizer.step()
+        return out
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if n > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 1)):
+        one_step(dev_ids)
+    sync_all()
+
+    sampler = ClockSampler(smp.local_rank())
+    if smp.rank() == 0:
+        sampler.start()
+    # ---- phase A: device-resident batch, CUDA events
+    N.reset_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    e0.record()
+    for _ in range(args.steps):
+        out = one_step(dev_ids)
+    e1.record()
+    sync_all()
+    ms_a = e0.elapsed_time(e1) / args.steps
+    launches = N.launches()
+    # ---- phase B: end to end (pinned host ids -> device every step, loss read back every step)
+    sync_all()
+    t0 = time.perf_counter()
+    e0.record()
+    last = None
+    for i in range(args.steps):
+        ids = host_ids[i % len(host_ids)].to(dev, non_blocking=True)
+        out = one_step(ids)
+        last = float(out.reduce_mean().item())
+    e1.record()
+    sync_all()
+    ms_b = e0.elapsed_time(e1) / args.steps
+    wall_b = (time.perf_counter() - t0) * 1000 / args.steps
+    clocks = sampler.stop() if smp.rank() == 0 else None
+
+    t = torch.tensor([ms_a, max(ms_b, wall_b)], device=dev, dtype=torch.float64)
+    if n > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_a, ms_b = float(t[0]), float(t[1])
+    if smp.rank() == 0:
+        value = tokens_per_step / (ms_a / 1000)
+        e2e = tokens_per_step / (ms_b / 1000)
+        flops = train_flops_per_token(mcfg, seq) * (4.0 / 3.0 if use_ckpt else 1.0)
+        line = {
+            "metric": "training tokens/sec (device-timed, max over ranks), GPT-J-6B bf16 seq 2048",
+            "value": round(value, 1), "unit": "tokens/s", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms_a, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic tokens, random-init weights",
+            "impl": "baseline-nccl-cublas" if baseline else "b200",
+            "config": {"model": args.model, "params": param_count(mcfg), "layers": mcfg["num_layers"],
+                       "global_batch": global_batch, "seq_len": seq, "microbatches": nmb, "micro_batch": micro,
+                       "parallelism": label, "activation_checkpointing": bool(use_ckpt), "optimizer": "AdamW fp32 master",
+                       "l2": "working set (12 GB of bf16 weights per step) >> 126 MB L2; no explicit flush needed",
+                       "valid": not bool(args.layers)},
+            "model_tflops_per_gpu": round(value * flops / n / 1e12, 1),
+            "clocks": clocks,
+            "e2e": {"value": round(e2e, 1), "unit": "tokens/s", "h2d_bytes_per_step": per_rank_batch * seq * 8,
+                    "d2h_bytes_per_step": 4 * nmb, "ms_per_step": round(ms_b, 2), "last_loss": last},
+            "gpu_launches": launches,
+            "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 1),
+        }
+        print(json.dumps(line), flush=True)
+    sync_all()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -103,7 +103,6 @@ class DistributedModel(nn.Module):
 
         # 3. name the tree
         mm.name_modules_and_create_parent_map(self.module)
-        self._param_names = {p: n for n, p in self.module.named_parameters()}
 
         # 4. partition now when there is nothing to decide (pp == 1); otherwise at the first step
         if cfg.pipeline_parallel_degree == 1:
@@ -359,6 +358,8 @@ class DistributedModel(nn.Module):
         return not getattr(param, "_smp_nonlocal", False)
 
     def get_param_name(self, param):
+        if getattr(self, "_param_names", None) is None or param not in self._param_names:
+            self._param_names = {p: n for n, p in self.module.named_parameters()}
         return self._param_names.get(param)
 
     def distributed_modules(self):

@@ -176,6 +176,10 @@ class DistributedAttentionLayer(DistributedModule):
         if self.use_normal_initialization:
             nn.init.normal_(self.qkv_weight, 0.0, std)
             nn.init.normal_(self.dense_weight, 0.0, std)
+            if self.qkv_bias is not None:
+                nn.init.zeros_(self.qkv_bias)
+            if self.dense_bias is not None:
+                nn.init.zeros_(self.dense_bias)
         else:
             # nn.Linear default (kaiming uniform with a=sqrt(5)) seen at full, unsplit size
             la, H = self.local_attention_size, self.hidden_size
@@ -303,15 +307,7 @@ class DistributedTransformerOutputLayer(DistributedModule):
             with initialize_with_input_partition(self, exclude_from_dist=["dense2_bias"]):
                 self.dense2_weight = nn.Parameter(torch.empty(H, li))
                 self.dense2_bias = nn.Parameter(torch.zeros(H)) if tp_rank() == 0 else None
-            if self.use_normal_initialization:
-                nn.init.normal_(self.dense1_weight, 0.0, self.initializer_range)
-                nn.init.normal_(self.dense2_weight, 0.0, self.initializer_range)
-            else:
-                nn.init.kaiming_uniform_(self.dense1_weight, a=math.sqrt(5))
-                nn.init.kaiming_uniform_(self.dense2_weight, a=math.sqrt(5))
-                nn.init.uniform_(self.dense1_bias, -1.0 / math.sqrt(H), 1.0 / math.sqrt(H))
-                if self.dense2_bias is not None:
-                    nn.init.uniform_(self.dense2_bias, -1.0 / math.sqrt(I), 1.0 / math.sqrt(I))
+            self._init_weights()
         with parameter_creation_scope(self, scaled_batch=False, dtype=dtype):
             mixed = bool(self.fp32_residual_addition)
             self.pre_layernorm_mod = FusedLayerNorm(H, self.layernorm_epsilon, mixed_dtype=mixed) \
@@ -336,6 +332,21 @@ class DistributedTransformerOutputLayer(DistributedModule):
 
         self._register_state_dict_hook(save_hook)
         self._register_load_state_dict_pre_hook(load_hook)
+
+    def _init_weights(self):
+        H, I = self.hidden_size, self.intermediate_size
+        if self.use_normal_initialization:
+            nn.init.normal_(self.dense1_weight, 0.0, self.initializer_range)
+            nn.init.normal_(self.dense2_weight, 0.0, self.initializer_range)
+            nn.init.zeros_(self.dense1_bias)
+            if self.dense2_bias is not None:
+                nn.init.zeros_(self.dense2_bias)
+        else:
+            nn.init.kaiming_uniform_(self.dense1_weight, a=math.sqrt(5))
+            nn.init.kaiming_uniform_(self.dense2_weight, a=math.sqrt(5))
+            nn.init.uniform_(self.dense1_bias, -1.0 / math.sqrt(H), 1.0 / math.sqrt(H))
+            if self.dense2_bias is not None:
+                nn.init.uniform_(self.dense2_bias, -1.0 / math.sqrt(I), 1.0 / math.sqrt(I))
 
     def state_dict_layout(self):
         sz = self.all_local_intermediate_sizes
