@@ -270,3 +270,65 @@ SMPK_API int smpk_head_transpose(void* stream, const void* src, void* dst, int d
   SMPK_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Column sums without any caller-supplied or library-allocated scratch.
+//
+// Who this is for: callers that reach this library through the plain C ABI and have no allocator to
+// lean on - a C / Fortran / ctypes host program without torch's workspace cache, a plugin living inside
+// another framework that has already claimed the whole device for its own pool (a raw cudaMalloc then
+// fails even though that pool has room), or latency-sensitive code that must not trigger the
+// device-wide synchronisation cudaMalloc and cudaFree imply.  smpk_colsum() asks such callers for a
+// scratch pointer they cannot produce; this variant keeps the scratch inside the library instead.
+//
+// The scratch is the file-scope device array below: CS_SPLITS x SMPK_COLSUM_STATIC_MAX_N floats
+// (64 x 8192 x 4 B = 2 MiB).  Every GPU that loads the library holds those 2 MiB until the process exits.
+// Nothing is allocated or freed here, and no allocating routine (cudaMalloc*, cudaFree*, torch) is called.
+//
+// Set-up: the first call on each device resolves the array's device address with
+// cudaGetSymbolAddress (in host code the array's name is only a stand-in, not an address a kernel
+// can use).  Make that first call before starting any stream capture on that device.
+//
+// Sharing: every call on a device uses the same array, which keeps whatever the previous call left in
+// it.  Each call overwrites every partial-sum slot it later reads (rows [0, splits) x columns [0, N)),
+// so nothing needs to start at zero and stale contents are never observed.  Two calls that overlap on
+// the GPU (different streams, or different host threads) race on the array - serialise them.
+#define SMPK_COLSUM_STATIC_MAX_N 8192
+
+static __device__ __align__(256) float g_colsum_static_scratch[CS_SPLITS * SMPK_COLSUM_STATIC_MAX_N];
+
+SMPK_API int smpk_colsum_static_max_n() { return SMPK_COLSUM_STATIC_MAX_N; }
+
+SMPK_API int smpk_colsum_static(void* stream, const void* x, int dtype, int rows, int N, long long ld, void* out,
+                                int out_dtype, int accumulate) {
+  static float* dev_ptr[64] = {nullptr};
+  SMPK_REQUIRE(N >= 0 && rows >= 0, "colsum_static: negative shape rows=%d N=%d", rows, N);
+  SMPK_REQUIRE(N <= SMPK_COLSUM_STATIC_MAX_N,
+               "colsum_static: N=%d exceeds the built-in scratch (max N = %d); use smpk_colsum with your own scratch",
+               N, SMPK_COLSUM_STATIC_MAX_N);
+  if (N == 0) return 0;
+  int dev = 0;
+  SMPK_CHECK_CUDA(cudaGetDevice(&dev));
+  SMPK_REQUIRE(dev >= 0 && dev < 64, "colsum_static: device index %d out of range", dev);
+  if (dev_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    SMPK_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_static_scratch));
+    SMPK_REQUIRE(p != nullptr, "colsum_static: cudaGetSymbolAddress returned a null address");
+    dev_ptr[dev] = p;
+  }
+  float* scratch = dev_ptr[dev];
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int nsplit = rows < CS_SPLITS ? (rows > 0 ? rows : 1) : CS_SPLITS;
+  const bool vec = (N % 8 == 0) && (ld % 8 == 0) && aligned16(x);
+  if (vec) {
+    dim3 grid((N / 8 + 31) / 32, nsplit), block(32, 16);
+    colsum_partial_kernel<<<grid, block, 0, s>>>(x, dtype, rows, N, ld, scratch);
+  } else {
+    dim3 grid((N + 127) / 128, nsplit);
+    colsum_scalar_partial_kernel<<<grid, 128, 0, s>>>(x, dtype, rows, N, ld, scratch);
+  }
+  SMPK_CHECK_CUDA(cudaGetLastError());
+  colsum_fold_kernel<<<(N + 127) / 128, 128, 0, s>>>(scratch, nsplit, N, out, out_dtype, accumulate);
+  SMPK_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -78,6 +78,15 @@ int smpk_bias_gelu(void* stream, const void* x, const void* bias, int bias_dtype
 int smpk_colsum_scratch_floats(int N);
 int smpk_colsum(void* stream, const void* x, int dtype, int rows, int N, long long ld, void* out, int out_dtype,
                 int accumulate, float* scratch);
+/* Column sums with the scratch held inside the library (a 2 MiB static device array per GPU) for callers
+ * that cannot allocate: bare C-ABI hosts with no workspace cache, plugins inside a process whose device
+ * memory is fully owned by another pool, code that must avoid cudaMalloc's device-wide synchronisation.
+ * Same result as smpk_colsum.  N must be <= smpk_colsum_static_max_n() (8192), else an error is returned.
+ * The first call on a device resolves the array's address (make it before any stream capture); calls that
+ * overlap on one GPU race on the shared array.  No counterpart in the reference. */
+int smpk_colsum_static_max_n(void);
+int smpk_colsum_static(void* stream, const void* x, int dtype, int rows, int N, long long ld, void* out,
+                       int out_dtype, int accumulate);
 int smpk_qkv_rotary(void* stream, void* fused, void* q, void* k, void* v, int dtype, const float* cosT,
                     const float* sinT, int B, int S, int heads, int d, int rot, int style, int pos_offset, int merge,
                     long long fused_ld);
