@@ -1,0 +1,98 @@
+"""Control messages of the pipeline engine and the tensor (de)stubbing around them.
+
+Same vocabulary as the reference's request / result dataclasses (reference smdistributed/modelparallel/
+torch/messages.py:48-520: ModuleExecutionRequest, ForwardExecutionResult, BackwardExecutionResult,
+MicrobatchEndResult, ...), trimmed to what a request/response protocol with segment-wise backward needs.
+A message is a small picklable object sent on the bus' server channel; tensors inside arguments are
+replaced by ``TensorStub`` (shape / dtype / requires_grad) and travel separately over NCCL or gloo p2p
+in the order of their stub indices (reference torch/serialization.py:40-68, 283-363).
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Any
+
+import torch
+
+from ..backend.split import map_structure
+
+
+@dataclass(frozen=True)
+class TensorStub:
+    index: int
+    shape: tuple
+    dtype: torch.dtype
+    requires_grad: bool
+
+
+def stubify(obj):
+    """Returns (skeleton, tensors): tensors replaced by stubs, listed in stub order."""
+    tensors = []
+
+    def f(x):
+        if torch.is_tensor(x):
+            tensors.append(x)
+            return TensorStub(len(tensors) - 1, tuple(x.shape), x.dtype, bool(x.requires_grad))
+        return x
+
+    return map_structure(f, obj), tensors
+
+
+def destubify(skel, tensors):
+    return map_structure(lambda x: tensors[x.index] if isinstance(x, TensorStub) else x, skel)
+
+
+def stubs_of(skel):
+    out = []
+    map_structure(lambda x: out.append(x) if isinstance(x, TensorStub) else None, skel)
+    return sorted(out, key=lambda s: s.index)
+
+
+@dataclass
+class ForwardRequest:
+    """Execute ``module_name`` on its owner for microbatch ``mb`` (reference ModuleExecutionRequest)."""
+    mb: int
+    call_id: tuple
+    module_name: str
+    skeleton: Any                 # (args, kwargs) with TensorStubs
+    grad_enabled: bool
+    requester: int                # global rank
+
+
+@dataclass
+class ForwardResult:
+    mb: int
+    call_id: tuple
+    skeleton: Any                 # outputs with TensorStubs
+    error: str | None = None
+
+
+@dataclass
+class BackwardRequest:
+    """Gradients w.r.t. the outputs of a remote call; ``grad_present[i]`` tells which output stubs have one."""
+    mb: int
+    call_id: tuple
+    grad_meta: list               # [(index, shape, dtype)] for the gradients that follow on p2p
+    requester: int
+
+
+@dataclass
+class BackwardResult:
+    mb: int
+    call_id: tuple
+    grad_meta: list               # [(input stub index, shape, dtype)] gradients w.r.t. the call's inputs
+    error: str | None = None
+
+
+@dataclass
+class StepDone:
+    """Leader -> followers: every microbatch finished; carries the step function's (detached) outputs."""
+    step: int
+    outputs: Any = None
+
+
+@dataclass
+class PartitionInfo:
+    """Leader -> everyone on the first step: module name -> pipeline rank."""
+    assignment: dict = field(default_factory=dict)

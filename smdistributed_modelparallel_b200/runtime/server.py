@@ -1,0 +1,487 @@
+"""Pipeline-parallel execution engine.
+
+Semantics follow the reference's module server (reference smdistributed/modelparallel/torch/server.py:
+145-478, worker.py:144-520, patches/execution.py:165-440, ops.py:226-388, sequential.py:94-281): any
+``nn.Module`` of the tree may live on any pipeline rank; the step function runs on pp_rank 0 of each
+pipeline group (the leader); when execution reaches a module owned by another rank, a request carries
+the arguments there, the owner runs the module (recursively dispatching *its* remote children) and
+returns the outputs; backward crosses the same boundaries in reverse.  Runs of consecutive
+``nn.Sequential`` children on one rank travel as a single request.
+
+What is different (by design):
+
+* **No worker threads.**  A task that must wait (for a forward result, a backward result) pumps the
+  message bus re-entrantly: incoming requests are served on the same Python stack, and the leader may
+  start the next microbatch while it waits - that is what fills the pipeline.  One thread, no
+  condition-variable hand-offs, deterministic order.
+* **Segment-wise backward.**  Outputs of a remote call enter the caller's autograd graph as leaves.
+  ``model.backward`` runs autograd on the local segment; gradients that reach a boundary leaf are
+  shipped to the owner, which back-propagates its own segment and returns the gradients of the call's
+  inputs; the caller then continues from those inputs.  Nothing ever blocks inside the autograd
+  engine, and gradient contributions from several paths simply accumulate (linearity), which is what
+  the reference's GradCounter / dummy-backward bookkeeping (server.py:162-252) works to guarantee.
+* ``model.backward`` inside the step function *registers* the backward; the engine schedules it by the
+  pipeline policy (``simple``: after all forwards; ``interleaved``: as soon as possible, before new
+  forwards) within the ``active_microbatches`` budget.
+* Activations and gradients cross ranks with NCCL (gloo on CPU) point-to-point on one dedicated 2-rank
+  communicator per direction; the control messages ride the TCP bus of libsmpb200_core.so.
+"""
+
+from __future__ import annotations
+
+import traceback
+from dataclasses import dataclass, field
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from ..backend.exceptions import PipelineParallelBWDError, SMPRuntimeError
+from ..backend.logger import get_logger
+from ..backend.split import map_structure
+from .messages import (BackwardRequest, BackwardResult, ForwardRequest, ForwardResult, StepDone, destubify,
+                       stubify, stubs_of)
+from .pipeline import MbStatus
+
+
+@dataclass
+class ExecRecord:
+    """Executor side: what a served forward call left behind for its backward."""
+    mb: int
+    input_leaves: list            # leaves created from received tensors (requires_grad per stub)
+    outputs: list                 # output tensors attached to the local graph
+    requester: int
+
+
+@dataclass
+class Boundary:
+    """Requester side: one remote call made while running microbatch ``mb``."""
+    mb: int
+    call_id: tuple
+    owner: int                    # global rank that executed the call
+    out_leaves: list              # leaves standing for the remote outputs in the local graph
+    in_tensors: list              # the argument tensors (attached to the local graph) in stub order
+    in_requires: list
+
+
+class PipelineP2P:
+    """Tensor transport between pipeline ranks: one 2-rank group per ordered (src, dst) pair."""
+
+    def __init__(self, state):
+        self.state = state
+        self.me = state.core.rank()
+        self._inflight = []
+
+    def _wire(self, t):
+        t = t.detach()
+        if t.dtype == torch.bool:
+            t = t.to(torch.uint8)
+        return t if t.is_contiguous() else t.contiguous()
+
+    def send(self, tensors, dst):
+        group = self.state.pp_p2p_groups[(self.me, dst)]
+        nbytes = 0
+        for t in tensors:
+            w = self._wire(t)
+            work = dist.isend(w, dst=dst, group=group)
+            self._inflight.append((work, w))
+            nbytes += w.numel() * w.element_size()
+        self.state.module_manager.record_hop(nbytes)
+        self._reap()
+
+    def recv(self, metas, src, device):
+        """metas: [(shape, dtype)] -> list of tensors (waits for arrival on the current stream)."""
+        group = self.state.pp_p2p_groups[(src, self.me)]
+        out, works = [], []
+        for shape, dtype in metas:
+            wire_dtype = torch.uint8 if dtype == torch.bool else dtype
+            buf = torch.empty(shape, dtype=wire_dtype, device=device)
+            works.append(dist.irecv(buf, src=src, group=group))
+            out.append(buf)
+        for w in works:
+            w.wait()
+        return [b.to(torch.bool) if dt == torch.bool else b for b, (_, dt) in zip(out, metas)]
+
+    def _reap(self):
+        self._inflight = [(w, t) for (w, t) in self._inflight if not w.is_completed()]
+
+    def drain(self):
+        for w, _ in self._inflight:
+            w.wait()
+        self._inflight = []
+
+
+class ExecutionServer:
+    def __init__(self, model):
+        from ..state_mod import state
+
+        self.state = state
+        self.model = model
+        self.core = state.core
+        self.comm = state.comm
+        self.me = self.core.rank()
+        self.pp_rank = self.core.pp_rank()
+        self.is_leader = self.pp_rank == 0
+        self.p2p = PipelineP2P(state)
+        self.partitioned = False
+        self.records: dict = {}            # call_id -> ExecRecord (executor side)
+        self.boundaries: dict = {}         # mb -> [Boundary] (requester side)
+        self.stash: dict = {}              # ("F"|"B", call_id) -> (msg, tensors)
+        self.deferred_bwd: dict = {}       # mb -> (tensors, grads)
+        self._counter = 0
+        self._step = 0
+        self._step_ctx = None
+        self._done_msg = None
+        self._orig_forward = {}
+
+    # ================================================================== partitioning (first step)
+    def _partition(self):
+        from ..pipeline.partition import partition_model
+
+        st = self.state
+        mm = st.module_manager
+        assignment = partition_model(self.model.module, mm, st.cfg)
+        # every rank computes the same deterministic assignment; the leader's copy is authoritative
+        if self.core.pp_size() > 1:
+            if self.is_leader:
+                for r in self.core.get_pp_group():
+                    if r != self.me:
+                        self.comm.server_send(("partition", assignment), r)
+            else:
+                while True:
+                    src, tx, obj = self.comm.server_next_message(-1)
+                    if isinstance(obj, tuple) and obj and obj[0] == "partition":
+                        assignment = obj[1]
+                        break
+        mm.assign_partitions(assignment)
+        self.model.post_partition()
+        self._install_dispatchers()
+        self.partitioned = True
+        if self.core.rank() == 0:
+            by_rank = {}
+            for n, r in assignment.items():
+                by_rank.setdefault(r, 0)
+                by_rank[r] += 1
+            get_logger().info(f"pipeline partition: modules per rank {dict(sorted(by_rank.items()))}")
+
+    def _owner_rank(self, module) -> int:
+        return self.core.pp_rank_to_rank(self.state.module_manager.get_partition(module))
+
+    def _install_dispatchers(self):
+        mm = self.state.module_manager
+        root = self.model.module
+        part = mm.get_partition
+
+        def mixed_sequential(m):
+            if not isinstance(m, nn.Sequential):
+                return False
+            ranks = {part(c) for c in m.children()}
+            return len(ranks) > 1 or (ranks and ranks != {part(m)})
+
+        seqs = {m for m in root.modules() if mixed_sequential(m)}
+        for m in seqs:
+            self._orig_forward[m] = m.forward
+            m.forward = self._make_sequential_forward(m)
+        for parent in root.modules():
+            if parent in seqs:
+                continue            # children of a mixed Sequential are dispatched chunk-wise by its forward
+            for child in parent.children():
+                if child in seqs or child in self._orig_forward:
+                    continue
+                if part(child) != part(parent):
+                    self._orig_forward[child] = child.forward
+                    child.forward = self._make_dispatch_forward(child)
+
+    def _make_dispatch_forward(self, module):
+        orig = self._orig_forward[module]
+        name = self.state.module_manager.get_module_name(module)
+
+        def forward(*args, **kwargs):
+            if self.state.module_manager.get_partition(module) == self.pp_rank:
+                return orig(*args, **kwargs)
+            return self._remote_forward(name, None, self._owner_rank(module), args, kwargs)
+
+        return forward
+
+    def _make_sequential_forward(self, seq):
+        name = self.state.module_manager.get_module_name(seq)
+        part = self.state.module_manager.get_partition
+
+        def forward(inp):
+            kids = list(seq.children())
+            i, n = 0, len(kids)
+            while i < n:
+                r = part(kids[i])
+                j = i
+                while j < n and part(kids[j]) == r:
+                    j += 1
+                if r == self.pp_rank:
+                    for c in kids[i:j]:
+                        inp = c(inp)
+                else:
+                    inp = self._remote_forward(name, (i, j), self.core.pp_rank_to_rank(r), (inp,), {})
+                i = j
+            return inp
+
+        return forward
+
+    def _run_local(self, module_name, span, args, kwargs):
+        mm = self.state.module_manager
+        m = mm.get_module(module_name)
+        if span is not None:
+            x = args[0]
+            for c in list(m.children())[span[0]:span[1]]:
+                x = c(x)
+            return x
+        return m(*args, **kwargs)     # the dispatcher sees partition == this rank and runs the real forward
+
+    # ================================================================== message pump
+    def _new_call_id(self, mb):
+        self._counter += 1
+        return (self.me, mb, self._counter)
+
+    def _pump_one(self, timeout_ms) -> bool:
+        """Handle one incoming control message; False if none arrived within the timeout."""
+        got = self.comm.server_next_message(timeout_ms)
+        if got is None:
+            return False
+        src, _tx, msg = got
+        self._handle(src, msg)
+        return True
+
+    def _handle(self, src, msg):
+        dev = self.state.device
+        if isinstance(msg, ForwardRequest):
+            metas = [(s.shape, s.dtype) for s in stubs_of(msg.skeleton)]
+            tensors = self.p2p.recv(metas, src, dev)
+            self._serve_forward(src, msg, tensors)
+        elif isinstance(msg, ForwardResult):
+            metas = [(s.shape, s.dtype) for s in stubs_of(msg.skeleton)] if msg.error is None else []
+            self.stash[("F", msg.call_id)] = (msg, self.p2p.recv(metas, src, dev))
+        elif isinstance(msg, BackwardRequest):
+            grads = self.p2p.recv([(shape, dt) for _, shape, dt in msg.grad_meta], src, dev)
+            self._serve_backward(src, msg, grads)
+        elif isinstance(msg, BackwardResult):
+            grads = self.p2p.recv([(shape, dt) for _, shape, dt in msg.grad_meta], src, dev) if msg.error is None else []
+            self.stash[("B", msg.call_id)] = (msg, grads)
+        elif isinstance(msg, StepDone):
+            self._done_msg = msg
+        elif isinstance(msg, tuple) and msg and msg[0] == "partition":
+            pass
+        else:
+            raise SMPRuntimeError(f"unexpected pipeline message {type(msg).__name__}")
+
+    def _wait_for(self, key):
+        """Block until stash[key] exists, serving requests (and, on the leader, starting further
+        microbatches) meanwhile."""
+        while key not in self.stash:
+            if self._pump_one(0):
+                continue
+            if self.is_leader and self._step_ctx is not None and self._start_nested_task():
+                continue
+            self._pump_one(20)
+        return self.stash.pop(key)
+
+    # ================================================================== forward across ranks
+    def _remote_forward(self, module_name, span, owner, args, kwargs):
+        st = self.state
+        mb = st.microbatch
+        skel, tensors = stubify((args, kwargs))
+        call_id = self._new_call_id(mb)
+        grad_on = torch.is_grad_enabled()
+        req = ForwardRequest(mb, call_id, module_name if span is None else (module_name, span), skel, grad_on, self.me)
+        self.core.timeline_record_pipeline_event(mb, f"fwd_req {module_name}")
+        self.comm.server_send(req, owner)
+        self.p2p.send(tensors, owner)
+        msg, outs = self._wait_for(("F", call_id))
+        st.microbatch = mb
+        if msg.error is not None:
+            raise SMPRuntimeError(f"remote execution of {module_name} on rank {owner} failed:\n{msg.error}")
+        leaves = []
+        for stub, t in zip(stubs_of(msg.skeleton), outs):
+            if grad_on and stub.requires_grad and t.is_floating_point():
+                t.requires_grad_(True)
+            leaves.append(t)
+        if grad_on:
+            self.boundaries.setdefault(mb, []).append(
+                Boundary(mb, call_id, owner, leaves, tensors, [bool(t.requires_grad) for t in tensors]))
+        return destubify(msg.skeleton, leaves)
+
+    def _serve_forward(self, src, req: ForwardRequest, tensors):
+        st = self.state
+        prev_mb = st.microbatch
+        st.microbatch = req.mb
+        name, span = (req.module_name, None) if isinstance(req.module_name, str) else req.module_name
+        try:
+            leaves = []
+            for stub, t in zip(stubs_of(req.skeleton), tensors):
+                if req.grad_enabled and stub.requires_grad and t.is_floating_point():
+                    t.requires_grad_(True)
+                leaves.append(t)
+            args, kwargs = destubify(req.skeleton, leaves)
+            self.core.timeline_record_pipeline_event(req.mb, f"fwd_exec {name}")
+            with torch.set_grad_enabled(req.grad_enabled):
+                out = self._run_local(name, span, args, kwargs)
+            skel, outs = stubify(out)
+            if req.grad_enabled:
+                self.records[req.call_id] = ExecRecord(req.mb, leaves, outs, src)
+            self.comm.server_send(ForwardResult(req.mb, req.call_id, skel), src)
+            self.p2p.send(outs, src)
+        except Exception:
+            self.comm.server_send(ForwardResult(req.mb, req.call_id, None, traceback.format_exc()), src)
+            raise
+        finally:
+            st.microbatch = prev_mb
+
+    # ================================================================== backward across ranks
+    def _backward_segment(self, mb, tensors, grads):
+        """Autograd over the local segment, then ship boundary gradients and continue from the returned
+        input gradients until nothing is outstanding."""
+        pairs = [(t, g) for t, g in zip(tensors, grads) if t.requires_grad and g is not None]
+        if pairs:
+            torch.autograd.backward([t for t, _ in pairs], [g for _, g in pairs], retain_graph=True)
+        outstanding = []
+        for b in self.boundaries.get(mb, []):
+            meta, send = [], []
+            for i, leaf in enumerate(b.out_leaves):
+                if leaf.requires_grad and leaf.grad is not None:
+                    meta.append((i, tuple(leaf.grad.shape), leaf.grad.dtype))
+                    send.append(leaf.grad)
+                    leaf.grad = None
+            if send:
+                self.comm.server_send(BackwardRequest(mb, b.call_id, meta, self.me), b.owner)
+                self.p2p.send(send, b.owner)
+                outstanding.append(b)
+        for b in outstanding:
+            msg, in_grads = self._wait_for(("B", b.call_id))
+            self.state.microbatch = mb
+            if msg.error is not None:
+                raise PipelineParallelBWDError(f"remote backward on rank {b.owner} failed:\n{msg.error}")
+            ts = [b.in_tensors[i] for i, _, _ in msg.grad_meta]
+            if ts:
+                self._backward_segment(mb, ts, in_grads)
+
+    def _serve_backward(self, src, req: BackwardRequest, grads):
+        st = self.state
+        prev_mb = st.microbatch
+        st.microbatch = req.mb
+        try:
+            rec = self.records.get(req.call_id)
+            if rec is None:
+                raise PipelineParallelBWDError(f"no forward record for call {req.call_id}")
+            outs = [rec.outputs[i] for i, _, _ in req.grad_meta]
+            self.core.timeline_record_pipeline_event(req.mb, "bwd_exec")
+            self._backward_segment(req.mb, outs, grads)
+            meta, send = [], []
+            for i, leaf in enumerate(rec.input_leaves):
+                if leaf.requires_grad and leaf.grad is not None:
+                    meta.append((i, tuple(leaf.grad.shape), leaf.grad.dtype))
+                    send.append(leaf.grad)
+                    leaf.grad = None
+            self.comm.server_send(BackwardResult(req.mb, req.call_id, meta), src)
+            self.p2p.send(send, src)
+        except Exception:
+            self.comm.server_send(BackwardResult(req.mb, req.call_id, [], traceback.format_exc()), src)
+            raise
+        finally:
+            st.microbatch = prev_mb
+
+    # ================================================================== DistributedModel entry points
+    def run_model_forward(self, model, args, kwargs):
+        root = model.module
+        mm = self.state.module_manager
+        if mm.get_partition(root) == self.pp_rank:
+            return root(*args, **kwargs)
+        return self._remote_forward(mm.get_module_name(root), None, self._owner_rank(root), args, kwargs)
+
+    def run_model_backward(self, model, tensors, grads):
+        """Called from inside the step function: register; the scheduler decides when it runs."""
+        mb = self.state.microbatch
+        self.deferred_bwd[mb] = (tuple(tensors), tuple(grads))
+
+    # ================================================================== the step
+    def _start_nested_task(self) -> bool:
+        ctx = self._step_ctx
+        if ctx is None or ctx["depth"] >= ctx["max_depth"]:
+            return False
+        return self._run_next_task(nested=True)
+
+    def _run_next_task(self, nested=False) -> bool:
+        ctx = self._step_ctx
+        pipe = self.state.pipeline
+        mb = pipe.get_next_microbatch()
+        if mb is None:
+            return False
+        status = pipe.get_status(mb)
+        if status is MbStatus.READY_FOR_FWD and pipe.in_flight() >= ctx["active"]:
+            # budget exhausted: only a backward may start now
+            mb = pipe.get_next_mb_with_status(MbStatus.READY_FOR_BWD)
+            if mb is None:
+                return False
+            status = MbStatus.READY_FOR_BWD
+        if nested and status is MbStatus.READY_FOR_BWD and not ctx["nested_backward"]:
+            return False
+        pipe.promote_status(mb)
+        ctx["depth"] += 1
+        try:
+            st = self.state
+            prev = st.microbatch
+            st.microbatch = mb
+            if status is MbStatus.READY_FOR_FWD:
+                self.core.timeline_record_pipeline_event(mb, "fwd_start")
+                fn, a, k = ctx["func"], ctx["args"][mb], ctx["kwargs"][mb]
+                out = fn(*a, **k)
+                ctx["outputs"][mb] = map_structure(lambda x: x.detach() if torch.is_tensor(x) else x, out) \
+                    if ctx["detach"] else out
+                if mb in self.deferred_bwd:
+                    pipe.mark_ready_for_backward(mb)
+                else:
+                    pipe.mark_done(mb)
+            else:
+                self.core.timeline_record_pipeline_event(mb, "bwd_start")
+                tensors, grads = self.deferred_bwd.pop(mb)
+                self._backward_segment(mb, tensors, grads)
+                self.boundaries.pop(mb, None)
+                pipe.mark_done(mb)
+                self.core.timeline_record_pipeline_event(mb, "bwd_end")
+            st.microbatch = prev
+        finally:
+            ctx["depth"] -= 1
+        return True
+
+    def run_step(self, step_fn, args, kwargs, num_mb):
+        st = self.state
+        if not self.partitioned:
+            self._partition()
+        self._done_msg = None
+        pipe = st.pipeline
+        pipe.init_step()
+        group = self.core.get_pp_group()
+        if self.is_leader:
+            a, k = step_fn.splitter.preprocess_args_all_mbs(args, kwargs, num_mb)
+            self._step_ctx = {"func": step_fn.func, "args": a, "kwargs": k, "outputs": [None] * num_mb,
+                              "detach": step_fn.detach_outputs, "depth": 0, "max_depth": max(1, st.cfg.active_microbatches),
+                              "active": st.cfg.active_microbatches, "nested_backward": st.cfg.pipeline == "interleaved"}
+            try:
+                while pipe.has_more_ticks():
+                    if not self._run_next_task():
+                        self._pump_one(20)
+                outputs = self._step_ctx["outputs"]
+            finally:
+                self._step_ctx = None
+            wire = map_structure(lambda x: x.cpu() if torch.is_tensor(x) else x, outputs)
+            for r in group:
+                if r != self.me:
+                    self.comm.server_send(StepDone(self._step, wire), r)
+        else:
+            while self._done_msg is None:
+                self._pump_one(50)
+            dev = st.device
+            outputs = map_structure(lambda x: x.to(dev) if torch.is_tensor(x) else x, self._done_msg.outputs)
+        self.p2p.drain()
+        self.records.clear()
+        self.boundaries.clear()
+        self.stash.clear()
+        self.deferred_bwd.clear()
+        self._step += 1
+        return outputs

@@ -1,0 +1,55 @@
+"""Multi-process test harness: run ``fn(rank, world, *args)`` in ``world`` fresh processes with a
+torchrun-like environment (gloo on CPU).  The reference has no such tier - everything distributed there
+needs MPI and GPUs; this is what lets pipeline / tensor / data parallel plumbing run in CI."""
+
+import os
+import socket
+import sys
+import traceback
+
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _entry(rank, world, port, fn, args, queue):
+    os.environ.update({"RANK": str(rank), "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank),
+                       "LOCAL_WORLD_SIZE": str(world), "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port),
+                       "SMP_LOG_LEVEL": os.environ.get("SMP_LOG_LEVEL", "warning"), "CUDA_VISIBLE_DEVICES": ""})
+    sys.path.insert(0, ROOT)
+    try:
+        out = fn(rank, world, *args)
+        queue.put((rank, "ok", out))
+    except Exception:
+        queue.put((rank, "err", traceback.format_exc()))
+        raise
+
+
+def run_distributed(fn, world, *args, timeout=240):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = {}
+    try:
+        for _ in range(world):
+            rank, status, payload = q.get(timeout=timeout)
+            if status != "ok":
+                raise AssertionError(f"rank {rank} failed:\n{payload}")
+            results[rank] = payload
+    finally:
+        for p in procs:
+            p.join(timeout=20)
+            if p.is_alive():
+                p.kill()
+    return [results[r] for r in range(world)]
