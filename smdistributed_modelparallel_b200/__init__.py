@@ -52,6 +52,7 @@ def init(config=None):
     from .patches import patch_manager
 
     patch_manager.patch_constructor()
+    state.tp_registry.register_builtin()
     if torch.cuda.is_available():
         torch.cuda.set_device(core.local_rank())
     if core.rank() == 0:

@@ -137,7 +137,7 @@ class DistributedModel(nn.Module):
                     if self.dtype is not None:
                         out = _cast_floating(out, self.dtype)
             memo[id(m)] = out
-            if out is m:
+            if out is m and not isinstance(m, DistributedModule):     # never look inside distributed modules
                 for name, child in list(m.named_children()):
                     new = convert(child)
                     if new is not child:
@@ -266,13 +266,19 @@ class DistributedModel(nn.Module):
             yield
         finally:
             if torch.is_grad_enabled() and self._partitioned:
+                opt = state.optimizer
+                shard = getattr(opt, "_opt_shard", None) if opt is not None else None
                 if self.sdp_engine is not None:
                     self.sdp_engine.reduce_epilogue(sync)
-                elif self.reducer is not None and sync:
-                    self.reducer.synchronize()
-                opt = state.optimizer
-                if opt is not None and sync and hasattr(opt, "update_master_grads") and self.sdp_engine is None:
-                    opt.update_master_grads()
+                elif shard is not None:
+                    if sync:
+                        shard.reduce_gradients()
+                        shard.check_overflow()
+                else:
+                    if self.reducer is not None and sync:
+                        self.reducer.synchronize()
+                    if opt is not None and sync and hasattr(opt, "update_master_grads"):
+                        opt.update_master_grads()
                 for hook in list(self._post_step_hooks.values()):
                     hook(self, opt)
             self._num_steps += 1

@@ -84,6 +84,8 @@ class DistributedOptimizer:
     # ------------------------------------------------------------------ training API
     def zero_grad(self, set_to_none: bool = True):
         self.model.zero_grad_buffer()
+        if self._opt_shard is not None:
+            return
         if self._bit16 is not None:
             self._bit16.zero_grad()
         else:
@@ -198,8 +200,11 @@ class DistributedOptimizer:
             return self.model.sdp_engine.load_optimizer_state_dict(sd)
         inner = sd.get("optimizer_state_dict", sd)
         inner = {k: v for k, v in inner.items() if not k.startswith("_smp_")}
+        shard_info = sd.get("optimizer_state_dict", sd).get("_smp_opt_shard")
         if "state" in inner and "param_groups" in inner:
             self.optimizer.load_state_dict(inner)
+        if shard_info is not None and self._opt_shard is not None:
+            self._opt_shard.load_shard_info(shard_info)
         fp16 = sd.get("fp16")
         if fp16 is not None and self._bit16 is not None:
             b = self._bit16

@@ -25,24 +25,33 @@ from ..nn.utils import is_scaled_batch_parameter
 
 
 class GradBuffer:
-    def __init__(self, params, device, dtype=torch.float32, pad_to: int = 1):
-        """params: iterable of unique trainable parameters (order = layout order inside each region)."""
+    def __init__(self, params, device, dtype=torch.float32, pad_to: int = 1, group_of=None):
+        """params: iterable of unique trainable parameters.  Layout: the "scaled_batch" region first, then
+        "default"; inside a region parameters are ordered by ``group_of(p)`` (optimizer param-group index,
+        used by optimizer-state sharding so that every (region, group) is one contiguous, padded segment)
+        and otherwise keep their given order."""
         params = [p for p in params if p.requires_grad]
-        scaled = [p for p in params if is_scaled_batch_parameter(p)]
-        rest = [p for p in params if not is_scaled_batch_parameter(p)]
+        group_of = group_of or (lambda p: 0)
         self.regions = {}
+        self.segments = {}            # (region, group) -> (start, end)
         self.offsets = {}
         self.params = []
         off = 0
-        for name, plist in (("scaled_batch", scaled), ("default", rest)):
+        for name, want in (("scaled_batch", True), ("default", False)):
+            plist = [p for p in params if bool(is_scaled_batch_parameter(p)) == want]
             start = off
-            for p in plist:
-                self.offsets[p] = off
-                off += p.numel()
-                off = (off + 7) // 8 * 8          # keep every view 32-byte aligned for vector kernels
-                self.params.append(p)
-            if pad_to > 1:
-                off = start + ((off - start + pad_to - 1) // pad_to) * pad_to
+            for g in sorted({group_of(p) for p in plist}):
+                seg_start = off
+                for p in plist:
+                    if group_of(p) != g:
+                        continue
+                    self.offsets[p] = off
+                    off += p.numel()
+                    off = (off + 7) // 8 * 8      # keep every view 32-byte aligned for vector kernels
+                    self.params.append(p)
+                if pad_to > 1:
+                    off = seg_start + ((off - seg_start + pad_to - 1) // pad_to) * pad_to
+                self.segments[(name, g)] = (seg_start, off)
             self.regions[name] = (start, off)
         self.numel = off
         self.buffer = torch.zeros(max(off, 1), dtype=dtype, device=device)
@@ -62,6 +71,7 @@ class GradBuffer:
     def release(self):
         for h in self._hooks:
             h.remove()
+        self._hooks = []
         for p in self.params:
             if hasattr(p, "main_grad"):
                 del p.main_grad

@@ -20,13 +20,38 @@ def _free_port():
     return p
 
 
+def _to_wire(obj):
+    """Tensors cross the process boundary as numpy arrays (torch's fd-passing breaks when the child exits)."""
+    import torch
+
+    if torch.is_tensor(obj):
+        return ("__tensor__", obj.detach().cpu().float().numpy(), str(obj.dtype))
+    if isinstance(obj, dict):
+        return {k: _to_wire(v) for k, v in obj.items()}
+    if isinstance(obj, (list, tuple)):
+        return type(obj)(_to_wire(v) for v in obj)
+    return obj
+
+
+def _from_wire(obj):
+    import torch
+
+    if isinstance(obj, tuple) and len(obj) == 3 and obj[0] == "__tensor__":
+        return torch.from_numpy(obj[1])
+    if isinstance(obj, dict):
+        return {k: _from_wire(v) for k, v in obj.items()}
+    if isinstance(obj, (list, tuple)):
+        return type(obj)(_from_wire(v) for v in obj)
+    return obj
+
+
 def _entry(rank, world, port, fn, args, queue):
     os.environ.update({"RANK": str(rank), "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank),
                        "LOCAL_WORLD_SIZE": str(world), "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port),
                        "SMP_LOG_LEVEL": os.environ.get("SMP_LOG_LEVEL", "warning"), "CUDA_VISIBLE_DEVICES": ""})
     sys.path.insert(0, ROOT)
     try:
-        out = fn(rank, world, *args)
+        out = _to_wire(fn(rank, world, *args))
         queue.put((rank, "ok", out))
     except Exception:
         queue.put((rank, "err", traceback.format_exc()))
@@ -46,7 +71,7 @@ def run_distributed(fn, world, *args, timeout=240):
             rank, status, payload = q.get(timeout=timeout)
             if status != "ok":
                 raise AssertionError(f"rank {rank} failed:\n{payload}")
-            results[rank] = payload
+            results[rank] = _from_wire(payload)
     finally:
         for p in procs:
             p.join(timeout=20)
