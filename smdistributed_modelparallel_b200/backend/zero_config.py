@@ -72,7 +72,7 @@ def validate_zero2d_config(d: dict, core) -> None:
     shard = int(z.get("zero2d_shard_size", 1))
     if shard < 1:
         raise SMPValidationError("zero2d_shard_size must be >= 1")
-    world = core.size() if core is not None else None
+    world = getattr(core, "_size", None) if core is not None else None
     if world is not None and world % shard != 0:
         raise SMPValidationError(
             f"sharded_data_parallel_degree ({shard}) must divide the number of processes ({world})")

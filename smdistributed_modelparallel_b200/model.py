@@ -419,6 +419,8 @@ class DistributedModel(nn.Module):
         """Parameters / buffers this rank holds, plus the metadata needed to reload under the same or a
         different tensor-parallel degree (reference model.py:1482-1528)."""
         self._validate_partitioned()
+        if self.sdp_engine is not None:
+            return self.sdp_engine._model_shard_dict()
         full = self.module.state_dict(prefix=prefix + "module.", keep_vars=keep_vars)
         if state.core.pp_size() > 1:
             local_prefixes = []
@@ -454,12 +456,19 @@ class DistributedModel(nn.Module):
         from .checkpoint_utils import gather_full_state_dict
 
         self._validate_partitioned()
+        if self.sdp_engine is not None:
+            return self.sdp_engine.full_state_dict()
         return gather_full_state_dict(self, prefix=prefix, cast_to_cpu=cast_to_cpu, gather_to_rank0=gather_to_rank0)
 
     def load_state_dict(self, state_dict, strict=True, same_partition_load=False, translate_function=None):
         from .checkpoint_utils import load_into_model
 
         def _do(model, _opt=None):
+            if model.sdp_engine is not None and not (isinstance(state_dict, dict) and state_dict.get("_smp_zero2d")):
+                sd = {k: v for k, v in state_dict.items() if not k.startswith("_smp_")}
+                if translate_function is not None:
+                    sd = translate_function(sd)
+                return model.sdp_engine.load_full_state_dict(sd, strict=strict)
             return load_into_model(model, state_dict, strict=strict, translate_function=translate_function)
 
         if not self._partitioned:

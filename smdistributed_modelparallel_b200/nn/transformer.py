@@ -577,6 +577,12 @@ class DistributedTransformerLMHead(DistributedModule):
             return {"lm_head.weight": (0, None), "lm_head.bias": (0, None)}
         return {}
 
+    def sdp_directly_used_parameters(self):
+        """Parameters of child modules that this module's own forward touches (tied LM head)."""
+        if self.add_lm_head and self.tie_input_output_embedding:
+            return [self.word_embedding.weight]
+        return []
+
     # ------------------------------------------------------------------
     def _head_weight(self):
         return self.word_embedding.weight if self.tie_input_output_embedding else self.lm_head_weight

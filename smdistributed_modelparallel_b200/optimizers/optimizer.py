@@ -56,7 +56,10 @@ class DistributedOptimizer:
             group["params"] = [p for p in group["params"] if id(p) in local]
         self._build_name_maps()
         if model.sdp_engine is not None:
-            model.sdp_engine.attach_optimizer(self.optimizer, clip=cfg.sdp_gradient_clipping)
+            model.sdp_engine.attach_optimizer(self.optimizer, clip=cfg.sdp_gradient_clipping,
+                                              static_loss_scale=self._static_loss_scale,
+                                              dynamic_loss_scale=self._dynamic_loss_scale,
+                                              dynamic_loss_args=self._dynamic_loss_args)
         elif cfg.fp16 or cfg.bf16:
             self._bit16 = Bit16_Optimizer(
                 self.optimizer, model=model, static_loss_scale=self._static_loss_scale if cfg.fp16 else 1.0,
@@ -84,7 +87,7 @@ class DistributedOptimizer:
     # ------------------------------------------------------------------ training API
     def zero_grad(self, set_to_none: bool = True):
         self.model.zero_grad_buffer()
-        if self._opt_shard is not None:
+        if self._opt_shard is not None or self.model.sdp_engine is not None:
             return
         if self._bit16 is not None:
             self._bit16.zero_grad()
