@@ -35,7 +35,36 @@ constexpr int GROUP_M = 8;    // L2-friendly raster: 8 m-blocks share one sweep 
 
 enum EpiMode : int { EPI_NONE = 0, EPI_GELU_TANH = 1, EPI_GELU_ERF = 2, EPI_DGELU_TANH = 3, EPI_DGELU_ERF = 4 };
 
+// Communication fused into the GEMM (tensor-parallel groups of up to 8 GPUs on one NVSwitch domain).
+//   COMM_AG: the A operand is the token all-gather of every rank's shard.  The first `comm_ctas` CTAs
+//            of the grid copy the peers' shards out of peer memory (P2P loads over NVLink) into this
+//            GPU's gathered buffer, 128-row block by block, publishing a flag per block; the GEMM CTAs
+//            start with the local shard and consume remote blocks as their flags appear.
+//   COMM_RS: the output is reduce-scattered over tokens.  The epilogue stores every tile straight into
+//            the staging slot of the rank that owns those rows (P2P stores), remote destinations first,
+//            and raises that rank's arrival flag once all tiles for it are written; a small reduce
+//            kernel on the owner sums the slots.
+enum CommMode : int { COMM_NONE = 0, COMM_AG = 1, COMM_RS = 2 };
+constexpr int MAX_RANKS = 8;
+
+struct CommParams {
+  int mode, nranks, rank, rows_per_rank, comm_ctas;
+  uint32_t epoch;
+  // all-gather of A
+  const void* peer_src[MAX_RANKS];     // peer j's gathered buffer (same layout as mine); I read its slot j
+  void* local_buf;                     // my gathered buffer [nranks * rows_per_rank, K]
+  long long row_bytes;                 // K * 2
+  uint32_t* blk_flags;                 // local [M / 128]: block landed (== epoch)
+  const uint32_t* ready_flags;         // local [nranks]: peer j's slot is final for this epoch (written by j)
+  uint32_t* peer_done[MAX_RANKS];      // peer j's done[nranks]; I set [rank] = epoch after copying its slot
+  uint32_t* counters;                  // local [nranks] scratch counters, zero between uses
+  // reduce-scatter of C
+  void* peer_stage[MAX_RANKS];         // rank d's staging [nranks][rows_per_rank][N]; I write slot `rank`
+  uint32_t* peer_arrived[MAX_RANKS];   // rank d's arrived[nranks]; I set [rank] = epoch when my tiles landed
+};
+
 struct GemmParams {
+  CommParams comm;
   int M, N, K, batch;
   int num_m, num_n, num_k;
   int a_mn_major, b_mn_major;
@@ -80,6 +109,37 @@ __device__ __forceinline__ void tile_coords(int t, const GemmParams& p, int& b, 
   const int in_group = r - group_id * group_size;
   m_blk = first_m + in_group % gsm;
   n_blk = in_group / gsm;
+}
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t v, bool sys) {
+  while ((int32_t)((sys ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - v) < 0) __nanosleep(64);
+}
+
+// Order m-blocks so communication overlaps compute: AG starts with the local shard and walks the ring;
+// RS finishes with the local shard (remote tiles leave first).
+__device__ __forceinline__ int permute_m_block(int m_blk, const GemmParams& p) {
+  const CommParams& c = p.comm;
+  if (c.mode == COMM_NONE) return m_blk;
+  const int mpr = c.rows_per_rank / BLOCK_M;
+  const int ci = m_blk / mpr, within = m_blk - ci * mpr;
+  const int chunk = (c.mode == COMM_AG) ? (c.rank + ci) % c.nranks : (c.rank + 1 + ci) % c.nranks;
+  return chunk * mpr + within;
 }
 
 template <typename T>
@@ -183,16 +243,68 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   const uint32_t tmem_base = *tmem_slot;
 
   const int total_tiles = p.batch * p.num_m * p.num_n;
+  const int n_comm = (p.comm.mode == COMM_AG) ? p.comm.comm_ctas : 0;
+  const int tile0 = (int)blockIdx.x - n_comm;          // first tile of this CTA (negative: a copy CTA)
+  const int tstride = (int)gridDim.x - n_comm;
 
-  if (warp == 0) {
+  if (tile0 < 0) {
+    // ===================================================================== all-gather copy CTA
+    // Pull the peers' shards over NVLink with 16-byte loads, block of 128 rows by block, ring order.
+    const CommParams& c = p.comm;
+    const int mpr = c.rows_per_rank / BLOCK_M;
+    const long long blk_bytes = (long long)BLOCK_M * c.row_bytes;
+    for (int ci = 1; ci < c.nranks; ++ci) {
+      const int src = (c.rank + ci) % c.nranks;
+      if (threadIdx.x == 0) spin_until_ge(&c.ready_flags[src], c.epoch, true);
+      __syncthreads();
+      for (int sb = blockIdx.x; sb < mpr; sb += n_comm) {
+        const long long off = ((long long)src * mpr + sb) * blk_bytes;
+        const uint4* from = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(c.peer_src[src]) + off);
+        uint4* to = reinterpret_cast<uint4*>(reinterpret_cast<char*>(c.local_buf) + off);
+        const long long nvec = blk_bytes >> 4;
+        for (long long i = threadIdx.x; i < nvec; i += 4 * NUM_THREADS) {
+          uint4 v0, v1, v2, v3;
+          const long long i1 = i + NUM_THREADS, i2 = i + 2 * NUM_THREADS, i3 = i + 3 * NUM_THREADS;
+          v0 = from[i];
+          if (i1 < nvec) v1 = from[i1];
+          if (i2 < nvec) v2 = from[i2];
+          if (i3 < nvec) v3 = from[i3];
+          to[i] = v0;
+          if (i1 < nvec) to[i1] = v1;
+          if (i2 < nvec) to[i2] = v2;
+          if (i3 < nvec) to[i3] = v3;
+        }
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) st_release_gpu(&c.blk_flags[src * mpr + sb], c.epoch);
+      }
+      // tell `src` that this GPU no longer reads its shard once every copy CTA is through
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        const uint32_t old = atomicAdd(&c.counters[src], 1u);
+        if (old == (uint32_t)n_comm - 1u) {
+          c.counters[src] = 0;
+          __threadfence_system();
+          st_release_sys(&c.peer_done[src][c.rank], c.epoch);
+        }
+      }
+    }
+  } else if (warp == 0) {
     // ===================================================================== TMA producer
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int t = tile0; t < total_tiles; t += tstride) {
         int b, m_blk, n_blk;
         tile_coords(t, p, b, m_blk, n_blk);
+        m_blk = permute_m_block(m_blk, p);
         const int m0 = m_blk * BLOCK_M, n0 = n_blk * BN;
+        if (p.comm.mode == COMM_AG && m0 / p.comm.rows_per_rank != p.comm.rank) {
+          // rows of a remote shard: wait until a copy CTA has landed this 128-row block, then make the
+          // generic-proxy writes visible to the TMA (async proxy) reads that follow
+          spin_until_ge(&p.comm.blk_flags[m_blk], p.comm.epoch, false);
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         for (int kb = 0; kb < p.num_k; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
@@ -234,7 +346,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int t = tile0; t < total_tiles; t += tstride) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
@@ -277,11 +389,21 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     const int b_es = (p.bias_dtype == SMPK_F32) ? 4 : 2;
     const bool bias_vec_ok = p.bias == nullptr || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
     (void)b_es;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    for (int t = tile0; t < total_tiles; t += tstride) {
       int b, m_blk, n_blk;
       tile_coords(t, p, b, m_blk, n_blk);
+      m_blk = permute_m_block(m_blk, p);
       const int row = m_blk * BLOCK_M + ew * 32 + lane;
       const int n0 = n_blk * BN;
+      // reduce-scatter: this tile's rows belong to rank `dest`; write into its staging slot for this rank
+      int dest = 0;
+      char* c_base = reinterpret_cast<char*>(p.C);
+      long long row_in_c = row;
+      if (p.comm.mode == COMM_RS) {
+        dest = (m_blk * BLOCK_M) / p.comm.rows_per_rank;
+        c_base = reinterpret_cast<char*>(p.comm.peer_stage[dest]);
+        row_in_c = (long long)p.comm.rank * p.comm.rows_per_rank + (row - (long long)dest * p.comm.rows_per_rank);
+      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t(ew * 32) << 16) + acc * BN;
@@ -303,7 +425,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] += bv[i];
           }
-          const long long coff = (long long)b * p.c_bs + (long long)row * p.ldc + col0;
+          const long long coff = (long long)b * p.c_bs + row_in_c * p.ldc + col0;
           if (p.R != nullptr) {
             float rv[32];
             const long long roff = (long long)b * p.r_bs + (long long)row * p.ldr + col0;
@@ -329,7 +451,22 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
               for (int i = 0; i < 32; ++i) v[i] = smpk::gelu_erf(v[i]);
             }
           }
-          store32_dyn(p.C, p.out_dtype, coff, v, full && c_vec_ok, nvalid);
+          store32_dyn(c_base, p.out_dtype, coff, v, full && c_vec_ok, nvalid);
+        }
+      }
+      if (p.comm.mode == COMM_RS) {
+        // publish: once every epilogue warp of every tile bound for `dest` has stored, raise its flag
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) {
+          const int mpr = p.comm.rows_per_rank / BLOCK_M;
+          const uint32_t expect = (uint32_t)(mpr * p.num_n * 4);
+          const uint32_t old = atomicAdd(&p.comm.counters[dest], 1u);
+          if (old == expect - 1u) {
+            p.comm.counters[dest] = 0;
+            __threadfence_system();
+            st_release_sys(&p.comm.peer_arrived[dest][p.comm.rank], p.comm.epoch);
+          }
         }
       }
       // all TMEM reads of this accumulator stage are done -> hand it back to the MMA warp
@@ -419,7 +556,15 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStre
   const int total = p.batch * p.num_m * p.num_n;
   int grid = smpk::num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
-  if (total < grid) grid = total;
+  if (p.comm.mode == COMM_AG) {
+    // copy CTAs + GEMM CTAs must all be co-resident (the GEMM CTAs wait on flags the copy CTAs raise)
+    int gemm_ctas = grid - p.comm.comm_ctas;
+    if (gemm_ctas < 1) return smpk::set_error("gemm_comm: comm_ctas=%d leaves no CTA for the GEMM", p.comm.comm_ctas);
+    if (total < gemm_ctas) gemm_ctas = total;
+    grid = gemm_ctas + p.comm.comm_ctas;
+  } else if (total < grid) {
+    grid = total;
+  }
   gemm_tcgen05_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
   SMPK_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -427,12 +572,58 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStre
 
 }  // namespace
 
+// Host-visible mirror of CommParams (include/smpb200_kernels.h: SmpkCommDesc).
+struct SmpkCommDesc {
+  int mode, nranks, rank, rows_per_rank, comm_ctas;
+  unsigned int epoch;
+  const void* peer_src[MAX_RANKS];
+  void* local_buf;
+  unsigned int* blk_flags;
+  const unsigned int* ready_flags;
+  unsigned int* peer_done[MAX_RANKS];
+  unsigned int* counters;
+  void* peer_stage[MAX_RANKS];
+  unsigned int* peer_arrived[MAX_RANKS];
+};
+
+static int gemm_impl(void* stream, int in_dtype, int out_dtype, int M, int N, int K, int batch, const void* A,
+                     int lda, long long a_bs, int a_mn_major, const void* B, int ldb, long long b_bs,
+                     int b_mn_major, void* C, int ldc, long long c_bs, const void* bias, int bias_dtype,
+                     const void* R, int ldr, long long r_bs, int r_dtype, void* aux, float alpha, float beta,
+                     int epi, int max_ctas, const SmpkCommDesc* comm);
+
 // See include/smpb200_kernels.h for the contract.
 SMPK_API int smpk_gemm(void* stream, int in_dtype, int out_dtype, int M, int N, int K, int batch, const void* A,
                        int lda, long long a_bs, int a_mn_major, const void* B, int ldb, long long b_bs,
                        int b_mn_major, void* C, int ldc, long long c_bs, const void* bias, int bias_dtype,
                        const void* R, int ldr, long long r_bs, int r_dtype, void* aux, float alpha, float beta,
                        int epi, int max_ctas) {
+  return gemm_impl(stream, in_dtype, out_dtype, M, N, K, batch, A, lda, a_bs, a_mn_major, B, ldb, b_bs, b_mn_major, C,
+                   ldc, c_bs, bias, bias_dtype, R, ldr, r_bs, r_dtype, aux, alpha, beta, epi, max_ctas, nullptr);
+}
+
+// GEMM fused with a tensor-parallel collective over NVLink peer memory (see CommMode above).
+SMPK_API int smpk_gemm_comm(void* stream, int in_dtype, int out_dtype, int M, int N, int K, const void* A, int lda,
+                            int a_mn_major, const void* B, int ldb, int b_mn_major, void* C, int ldc,
+                            const void* bias, int bias_dtype, const void* R, int ldr, int r_dtype, float beta,
+                            void* aux, float alpha, int epi, int max_ctas, const SmpkCommDesc* comm) {
+  SMPK_REQUIRE(comm != nullptr && (comm->mode == COMM_AG || comm->mode == COMM_RS), "gemm_comm: bad comm descriptor");
+  SMPK_REQUIRE(comm->nranks >= 2 && comm->nranks <= MAX_RANKS, "gemm_comm: nranks %d out of range", comm->nranks);
+  SMPK_REQUIRE(comm->rows_per_rank % BLOCK_M == 0 && comm->rows_per_rank * comm->nranks == M,
+               "gemm_comm: M=%d must be nranks x rows_per_rank with rows_per_rank %% 128 == 0 (got %d x %d)", M,
+               comm->nranks, comm->rows_per_rank);
+  SMPK_REQUIRE(comm->mode != COMM_RS || aux == nullptr, "gemm_comm: aux output is not supported with reduce-scatter");
+  SMPK_REQUIRE(comm->mode != COMM_AG || (comm->comm_ctas >= 1 && !a_mn_major),
+               "gemm_comm: all-gather mode needs comm_ctas >= 1 and a K-major A operand");
+  return gemm_impl(stream, in_dtype, out_dtype, M, N, K, 1, A, lda, 0, a_mn_major, B, ldb, 0, b_mn_major, C, ldc, 0, bias,
+                   bias_dtype, R, ldr, 0, r_dtype, aux, alpha, beta, epi, max_ctas, comm);
+}
+
+static int gemm_impl(void* stream, int in_dtype, int out_dtype, int M, int N, int K, int batch, const void* A,
+                     int lda, long long a_bs, int a_mn_major, const void* B, int ldb, long long b_bs,
+                     int b_mn_major, void* C, int ldc, long long c_bs, const void* bias, int bias_dtype,
+                     const void* R, int ldr, long long r_bs, int r_dtype, void* aux, float alpha, float beta,
+                     int epi, int max_ctas, const SmpkCommDesc* comm) {
   SMPK_REQUIRE(in_dtype == SMPK_BF16 || in_dtype == SMPK_F16, "smpk_gemm: inputs must be bf16 or fp16");
   SMPK_REQUIRE(M > 0 && N > 0 && K > 0 && batch > 0, "smpk_gemm: empty problem M=%d N=%d K=%d batch=%d", M, N, K, batch);
   SMPK_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && (a_bs % 8) == 0 && (b_bs % 8) == 0,
@@ -454,6 +645,18 @@ SMPK_API int smpk_gemm(void* stream, int in_dtype, int out_dtype, int M, int N, 
   p.bias = bias; p.bias_dtype = bias_dtype;
   p.alpha = alpha; p.beta = beta; p.epi = epi;
   p.idesc = (in_dtype == SMPK_BF16) ? 1u : 0u;  // format code, expanded in launch<>
+  if (comm != nullptr) {
+    CommParams& c = p.comm;
+    c.mode = comm->mode; c.nranks = comm->nranks; c.rank = comm->rank; c.rows_per_rank = comm->rows_per_rank;
+    c.comm_ctas = comm->comm_ctas; c.epoch = comm->epoch;
+    c.local_buf = comm->local_buf; c.row_bytes = (long long)K * 2;
+    c.blk_flags = comm->blk_flags; c.ready_flags = comm->ready_flags; c.counters = comm->counters;
+    for (int i = 0; i < MAX_RANKS; ++i) {
+      c.peer_src[i] = comm->peer_src[i]; c.peer_done[i] = comm->peer_done[i];
+      c.peer_stage[i] = comm->peer_stage[i]; c.peer_arrived[i] = comm->peer_arrived[i];
+    }
+    if (c.mode == COMM_RS) p.C = c.peer_stage[c.rank];
+  }
 
   const int BN = (N > 128) ? 256 : (N > 64 ? 128 : 64);
   CUtensorMap ta, tb;

@@ -58,6 +58,15 @@ int smpc_get_and_reset_memory_metrics(double* out4);
 int smpc_get_and_reset_alloc_metrics(long long* out2);
 int smpc_device_count(void);
 
+/* ---- symmetric (peer-addressable) memory over CUDA IPC (no counterpart among the reference's Python-visible
+ *      entry points; replaces NCCL for tensor-parallel traffic: torch/nn/utils.py:701-821) */
+const char* smpc_symm_last_error(void);
+int smpc_symm_alloc(long long bytes, void** dev_ptr, unsigned char* handle64_out);
+int smpc_symm_open(const unsigned char* handle64, void** peer_ptr);
+int smpc_symm_close(void* peer_ptr);
+int smpc_symm_free(void* dev_ptr);
+int smpc_symm_can_access_peer(int peer_device);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,6 +37,39 @@ int smpk_gemm(void* stream, int in_dtype, int out_dtype, int M, int N, int K, in
               long long c_bs, const void* bias, int bias_dtype, const void* R, int ldr, long long r_bs, int r_dtype,
               void* aux, float alpha, float beta, int epi, int max_ctas);
 
+/* ---- GEMM fused with a tensor-parallel collective over NVLink peer memory -------------------------------
+ * mode 1 (all-gather -> GEMM): A = [nranks * rows_per_rank, K] is this GPU's gathered buffer; the local shard is
+ *   already in its slot, the first comm_ctas CTAs copy the peers' shards out of peer memory block by block while
+ *   the remaining CTAs run the GEMM, local rows first.  mode 2 (GEMM -> reduce-scatter): tiles are stored into the
+ *   staging slot of the rank owning their rows (peer_stage[d] is [nranks][rows_per_rank][N]), remote first;
+ *   smpk_rs_reduce on the owner sums the slots.  Flags are uint32 epochs in peer memory.
+ * Replaces NCCL all-gather / all-reduce next to cuBLAS GEMMs at torch/nn/transformer.py:1436,1474,1522,1141 and
+ * torch/nn/utils.py:540-571,701-821. */
+typedef struct {
+  int mode, nranks, rank, rows_per_rank, comm_ctas;
+  unsigned int epoch;
+  const void* peer_src[8];
+  void* local_buf;
+  unsigned int* blk_flags;
+  const unsigned int* ready_flags;
+  unsigned int* peer_done[8];
+  unsigned int* counters;
+  void* peer_stage[8];
+  unsigned int* peer_arrived[8];
+} SmpkCommDesc;
+int smpk_gemm_comm(void* stream, int in_dtype, int out_dtype, int M, int N, int K, const void* A, int lda,
+                   int a_mn_major, const void* B, int ldb, int b_mn_major, void* C, int ldc, const void* bias,
+                   int bias_dtype, const void* R, int ldr, int r_dtype, float beta, void* aux, float alpha, int epi,
+                   int max_ctas, const SmpkCommDesc* comm);
+int smpk_flags_signal(void* stream, void* const* peer_flags, int n, int index, unsigned int value);
+int smpk_flags_wait(void* stream, const void* flags, int n, int skip, unsigned int value);
+int smpk_p2p_allgather(void* stream, void* const* peer_src, void* local_buf, long long slot_bytes,
+                       const void* ready_flags, void* const* peer_done, void* counters, int nranks, int rank,
+                       unsigned int epoch, int ctas);
+int smpk_rs_reduce(void* stream, const void* staging, const void* arrived, void* const* peer_reduced, void* counter,
+                   const void* residual, int res_dtype, const void* bias, int bias_dtype, void* out, int out_dtype,
+                   long long rows, int N, int nranks, int rank, int dtype, unsigned int epoch);
+
 /* ---- LayerNorm (Apex fused_layer_norm_cuda: torch/apex/normalization/fused_layer_norm.py:26-78) */
 int smpk_layernorm_fwd(void* stream, const void* x, const void* residual, void* sum_out, int x_dtype,
                        const void* gamma, const void* beta, int w_dtype, void* y, int y_dtype, float* mean, float* rstd,

@@ -59,6 +59,12 @@ _SIG = {
     "smpc_get_and_reset_memory_metrics": ([POINTER(c_double)], I),
     "smpc_get_and_reset_alloc_metrics": ([POINTER(L)], I),
     "smpc_device_count": ([], I),
+    "smpc_symm_last_error": ([], c_char_p),
+    "smpc_symm_alloc": ([L, POINTER(P), ctypes.c_char_p], I),
+    "smpc_symm_open": ([ctypes.c_char_p, POINTER(P)], I),
+    "smpc_symm_close": ([P], I),
+    "smpc_symm_free": ([P], I),
+    "smpc_symm_can_access_peer": ([I], I),
 }
 _OPTIONAL: dict = {}
 

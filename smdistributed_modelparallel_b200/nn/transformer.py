@@ -193,40 +193,28 @@ class DistributedAttentionLayer(DistributedModule):
                 bound = 1.0 / math.sqrt(self.num_attention_heads * self.attention_head_size)
                 nn.init.uniform_(self.dense_bias, -bound, bound)
 
-    # ---- pieces used by DistributedTransformerLayer for the parallel attention+MLP form
-    def attend(self, gathered, B, S, attention_mask, cross_gathered=None, cross_len=None):
-        """gathered: [T, H] all tokens of the tp group's batch (B sequences).  Returns the row-parallel
-        partial product [T, H] (to be reduce-scattered by the caller)."""
-        g = _group()
+    # ---- pieces (also used by DistributedTransformerLayer for the parallel attention+MLP form)
+    def attention_core(self, qkv, B, S, attention_mask):
+        """qkv [T, 3*local] for all T = B*S tokens of the tp group's batch -> context [T, local]."""
         la, hl, d = self.local_attention_size, self.local_attention_heads, self.attention_head_size
         rot = self.rotary_dim or 0
         style = 0 if not rot else (2 if self.gpt_neox_type_rotary else 1)
         cos = sin = None
-        if self.cross_attention:
-            q2 = tp_ops.column_parallel_linear(gathered, self.qkv_weight[:la],
-                                               None if self.qkv_bias is None else self.qkv_bias[:la], None, g, True)
-            kv = tp_ops.column_parallel_linear(cross_gathered, self.qkv_weight[la:],
-                                               None if self.qkv_bias is None else self.qkv_bias[la:], None, g, True)
-            q = A.tokens_to_heads(q2.reshape(B, S, la), hl)
-            k = A.tokens_to_heads(kv[:, :la].reshape(B, cross_len, la), hl)
-            v = A.tokens_to_heads(kv[:, la:].reshape(B, cross_len, la), hl)
-            causal = False
-        else:
-            qkv = tp_ops.column_parallel_linear(gathered, self.qkv_weight, self.qkv_bias, None, g, True)
-            if style:
-                cos, sin = A.rotary_tables(max(S, self.num_positions or S), rot, float(self.rotary_emb_base), qkv.device)
-            q, k, v = A.qkv_split_rotary(qkv, B, S, hl, d, rot, style, cos, sin, 0)
-            causal = self.causal_mask_size is not None
+        if style:
+            cos, sin = A.rotary_tables(max(S, self.num_positions or S), rot, float(self.rotary_emb_base), qkv.device)
+        q, k, v = A.qkv_split_rotary(qkv, B, S, hl, d, rot, style, cos, sin, 0)
+        causal = self.causal_mask_size is not None
+        return self._attend(q, k, v, B, S, causal, attention_mask)
+
+    def _attend(self, q, k, v, B, S, causal, attention_mask):
+        d, la = self.attention_head_size, self.local_attention_size
         scale = 1.0 / math.sqrt(d) if self.scale_attention_scores else 1.0
         if self.scale_attn_by_layer_idx and not self.query_key_layer_scaling:
             scale = scale / float(self.layer_idx + 1)
-        mask = None
-        if attention_mask is not None and not causal:
-            mask = attention_mask
+        mask = attention_mask if (attention_mask is not None and not causal) else None
         ctx = A.core_attention(q, k, v, causal=causal, mask=mask, scale=scale, dropout_p=self.attention_dropout_prob,
                                training=self.training, window=self.window_size if causal else None)
-        ctx2 = A.heads_to_tokens(ctx).reshape(B * S, la)
-        return tp_ops.row_parallel_linear(ctx2, self.dense_weight, self.dense_bias, g, scatter_output=False)
+        return A.heads_to_tokens(ctx).reshape(B * S, la)
 
     def forward(self, inp):
         """inp: (hidden [b, S, H], attention_mask) or (hidden, cross_states, attention_mask)."""
@@ -238,19 +226,27 @@ class DistributedAttentionLayer(DistributedModule):
         b, S, H = hidden.shape
         g = _group()
         t = tp_size()
+        la, hl = self.local_attention_size, self.local_attention_heads
         x2 = hidden.reshape(b * S, H)
         h = self.pre_layernorm_mod(x2) if self.pre_layernorm_mod is not None else x2
         if h.dtype != self.qkv_weight.dtype:
             h = h.to(self.qkv_weight.dtype)
-        gathered = tp_ops.GatherTokens.apply(h, g) if t > 1 else h
-        cross_g, clen = None, None
-        if cross_states is not None:
-            clen = cross_states.shape[1]
-            c2 = cross_states.reshape(-1, H)
-            cross_g = tp_ops.GatherTokens.apply(c2, g) if t > 1 else c2
         mask = _full_mask(attention_mask, b * t, g)
-        partial = self.attend(gathered, b * t, S, mask, cross_g, clen)
-        out = tp_ops.ScatterSumTokens.apply(partial, g) if t > 1 else partial
+        if cross_states is None:
+            qkv = tp_ops.ag_linear(h, self.qkv_weight, self.qkv_bias, None, g)
+            ctx2 = self.attention_core(qkv, b * t, S, mask)
+        else:
+            clen = cross_states.shape[1]
+            c2 = cross_states.reshape(-1, H).to(self.qkv_weight.dtype)
+            qb = None if self.qkv_bias is None else self.qkv_bias[:la]
+            kvb = None if self.qkv_bias is None else self.qkv_bias[la:]
+            q2 = tp_ops.ag_linear(h, self.qkv_weight[:la], qb, None, g)
+            kv = tp_ops.ag_linear(c2, self.qkv_weight[la:], kvb, None, g)
+            q = A.tokens_to_heads(q2.reshape(b * t, S, la), hl)
+            k = A.tokens_to_heads(kv[:, :la].reshape(b * t, clen, la), hl)
+            v = A.tokens_to_heads(kv[:, la:].reshape(b * t, clen, la), hl)
+            ctx2 = self._attend(q, k, v, b * t, S, False, mask)
+        out = tp_ops.linear_rs(ctx2, self.dense_weight, self.dense_bias, g)
         out = F.dropout(out, self.hidden_dropout_prob, self.training)
         out = out.to(x2.dtype) + x2
         if self.layernorm is not None:
@@ -353,28 +349,22 @@ class DistributedTransformerOutputLayer(DistributedModule):
         return {"dense1.weight": (0, sz), "dense1.bias": (0, sz), "dense2.weight": (1, sz),
                 "dense2.bias": ("one_rank", None)}
 
-    def mlp(self, gathered):
-        """gathered [T, H] -> row-parallel partial product [T, H]."""
-        g = _group()
-        mode = _gelu_mode(self.activation)
-        if mode is not None:
-            h = tp_ops.column_parallel_linear(gathered, self.dense1_weight, self.dense1_bias, mode, g, True)
-        else:
-            h = tp_ops.column_parallel_linear(gathered, self.dense1_weight, self.dense1_bias, None, g, True)
-            h = F.relu(h) if self.activation == "relu" else getattr(F, self.activation)(h)
-        return tp_ops.row_parallel_linear(h, self.dense2_weight, self.dense2_bias, g, scatter_output=False)
+    def _act_other(self, h):
+        return F.relu(h) if self.activation == "relu" else getattr(F, self.activation)(h)
 
     def forward(self, hidden):
         shape = hidden.shape
         H = shape[-1]
-        g, t = _group(), tp_size()
+        g = _group()
         x2 = hidden.reshape(-1, H)
         h = self.pre_layernorm_mod(x2) if self.pre_layernorm_mod is not None else x2
         if h.dtype != self.dense1_weight.dtype:
             h = h.to(self.dense1_weight.dtype)
-        gathered = tp_ops.GatherTokens.apply(h, g) if t > 1 else h
-        partial = self.mlp(gathered)
-        out = tp_ops.ScatterSumTokens.apply(partial, g) if t > 1 else partial
+        mode = _gelu_mode(self.activation)
+        inter = tp_ops.ag_linear(h, self.dense1_weight, self.dense1_bias, mode, g)
+        if mode is None:
+            inter = self._act_other(inter)
+        out = tp_ops.linear_rs(inter, self.dense2_weight, self.dense2_bias, g)
         out = F.dropout(out, self.hidden_dropout_prob, self.training)
         out = out.to(x2.dtype) + x2
         if self.layernorm is not None:
@@ -431,8 +421,9 @@ class DistributedTransformerLayer(DistributedModule):
         return hidden, attention_mask
 
     def _parallel_forward(self, hidden, attention_mask):
-        """x + attn(ln_a(x)) + mlp(ln_m(x)) with one reduce-scatter for the sum of both branches and, when the
-        LayerNorm is shared (GPT-J), one all-gather for both."""
+        """x + attn(ln_a(x)) + mlp(ln_m(x)).  The attention-dense partial product rides into the MLP's
+        second GEMM as an epilogue residual so a single reduce-scatter carries both branches; when the
+        LayerNorm is shared (GPT-J) one all-gather - fused into the QKV GEMM - feeds both branches."""
         b, S, H = hidden.shape
         g, t = _group(), tp_size()
         att, out = self.attention, self.output
@@ -440,16 +431,22 @@ class DistributedTransformerLayer(DistributedModule):
         wdtype = att.qkv_weight.dtype
         ha = att.pre_layernorm_mod(x2) if att.pre_layernorm_mod is not None else x2
         ha = ha.to(wdtype) if ha.dtype != wdtype else ha
-        ga = tp_ops.GatherTokens.apply(ha, g) if t > 1 else ha
-        if out.pre_layernorm_mod is not None:
+        mask = _full_mask(attention_mask, b * t, g)
+        mode = _gelu_mode(out.activation)
+        shared_ln = out.pre_layernorm_mod is None
+        if shared_ln:
+            qkv, xg = tp_ops.ag_linear(ha, att.qkv_weight, att.qkv_bias, None, g, want_gathered=True)
+            inter = tp_ops.ColumnParallelLinear.apply(xg, out.dense1_weight, out.dense1_bias, mode, g, True)
+        else:
+            qkv = tp_ops.ag_linear(ha, att.qkv_weight, att.qkv_bias, None, g)
             hm = out.pre_layernorm_mod(x2)
             hm = hm.to(wdtype) if hm.dtype != wdtype else hm
-            gm = tp_ops.GatherTokens.apply(hm, g) if t > 1 else hm
-        else:
-            gm = ga
-        mask = _full_mask(attention_mask, b * t, g)
-        partial = att.attend(ga, b * t, S, mask) + out.mlp(gm)
-        y = tp_ops.ScatterSumTokens.apply(partial, g) if t > 1 else partial
+            inter = tp_ops.ag_linear(hm, out.dense1_weight, out.dense1_bias, mode, g)
+        if mode is None:
+            inter = out._act_other(inter)
+        ctx2 = att.attention_core(qkv, b * t, S, mask)
+        p1 = tp_ops.RowParallelLinear.apply(ctx2, att.dense_weight, att.dense_bias, g, False)   # partial, not reduced
+        y = tp_ops.linear_rs(inter, out.dense2_weight, out.dense2_bias, g, residual_full=p1)
         y = F.dropout(y, self.hidden_dropout_prob, self.training)
         y = y.to(x2.dtype) + x2
         return y.reshape(b, S, H)

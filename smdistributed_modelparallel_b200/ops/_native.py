@@ -75,6 +75,11 @@ _SIGNATURES = {
     "smpk_mt_novograd": (_MT + [I, F, F, F, F, I, I, F, I, I, P, F, P], I),
     "smpk_mt_l2norm_scratch_floats": ([], I),
     "smpk_mt_l2norm": (_MT + [P, P, P, P, P], I),
+    "smpk_gemm_comm": ([P, I, I, I, I, I, P, I, I, P, I, I, P, I, P, I, P, I, I, F, P, F, I, I, P], I),
+    "smpk_flags_signal": ([P, P, I, I, ctypes.c_uint], I),
+    "smpk_flags_wait": ([P, P, I, I, ctypes.c_uint], I),
+    "smpk_p2p_allgather": ([P, P, P, L, P, P, P, I, I, ctypes.c_uint, I], I),
+    "smpk_rs_reduce": ([P, P, P, P, P, P, I, P, I, P, I, L, I, I, I, I, ctypes.c_uint], I),
 }
 
 # entry points added after the first release are optional at load time

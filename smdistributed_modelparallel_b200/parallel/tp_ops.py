@@ -205,3 +205,41 @@ def column_parallel_linear(x_local, weight, bias=None, activation=None, group=No
 
 def row_parallel_linear(x, weight, bias=None, group=None, scatter_output=True):
     return RowParallelLinear.apply(x, weight, bias, group, scatter_output)
+
+
+# ------------------------------------------------------------------------------------------------
+# Layer-level entry points: pick the fused peer-memory kernels when they apply, else NCCL + GEMM.
+def _fused_applicable(rows_local, *tensors):
+    if _comm_mode != "fused":
+        return False
+    from . import fused_tp
+    return fused_tp.available() and fused_tp.usable(rows_local, *tensors)
+
+
+def ag_linear(x_local, weight, bias=None, activation=None, group=None, want_gathered=False):
+    """Column-parallel linear on token-sharded input: y[T, N/t] = act(allgather(x_local) W^T + b).
+    With ``want_gathered`` also returns the gathered input (for a second GEMM on the same activations)."""
+    if _group_size(group) == 1:
+        y = ColumnParallelLinear.apply(x_local, weight, bias, activation, None, True)
+        return (y, x_local) if want_gathered else y
+    if _fused_applicable(x_local.shape[0], x_local, weight):
+        from . import fused_tp
+        return fused_tp.FusedAGLinear.apply(x_local, weight, bias, activation, want_gathered)
+    gathered = GatherTokens.apply(x_local, group)
+    y = ColumnParallelLinear.apply(gathered, weight, bias, activation, group, True)
+    return (y, gathered) if want_gathered else y
+
+
+def linear_rs(x, weight, bias=None, group=None, residual_full=None):
+    """Row-parallel linear with token-sharded output: y[T/t, N] = reduce_scatter(x W^T + b + residual_full)."""
+    n = _group_size(group)
+    if n == 1:
+        y = RowParallelLinear.apply(x, weight, bias, None, False)
+        return y if residual_full is None else y + residual_full
+    if _fused_applicable(x.shape[0] // n, x, weight, residual_full) and x.shape[0] % n == 0:
+        from . import fused_tp
+        return fused_tp.FusedLinearRS.apply(x, weight, bias, residual_full)
+    partial = RowParallelLinear.apply(x, weight, bias, group, False)
+    if residual_full is not None:
+        partial = partial + residual_full
+    return ScatterSumTokens.apply(partial, group)
