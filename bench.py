@@ -153,9 +153,8 @@ def main():
         conf["prescaled_batch"] = False
     os.environ.setdefault("SMP_LOG_LEVEL", "warning")
     smp.init(conf)
-    if baseline:
-        from smdistributed_modelparallel_b200 import baseline_mode
-        baseline_mode.enable()
+    from smdistributed_modelparallel_b200.parallel import tp_ops
+    tp_ops.set_comm_mode("nccl" if (baseline or os.environ.get("BENCH_TP_COMM") == "nccl") else "fused")
     dev = torch.device("cuda", smp.local_rank())
     torch.manual_seed(1234 + smp.rank())
 
@@ -243,7 +242,7 @@ def main():
             "impl": "baseline-nccl-cublas" if baseline else "b200",
             "config": {"model": args.model, "params": param_count(mcfg), "layers": mcfg["num_layers"],
                        "global_batch": global_batch, "seq_len": seq, "microbatches": nmb, "micro_batch": micro,
-                       "parallelism": label, "activation_checkpointing": bool(use_ckpt), "optimizer": "AdamW fp32 master",
+                       "parallelism": label, "tp_comm": tp_ops.get_comm_mode() if tp > 1 else None, "activation_checkpointing": bool(use_ckpt), "optimizer": "AdamW fp32 master",
                        "l2": "working set (12 GB of bf16 weights per step) >> 126 MB L2; no explicit flush needed",
                        "valid": not bool(args.layers)},
             "model_tflops_per_gpu": round(value * flops / n / 1e12, 1),

@@ -31,6 +31,7 @@ constexpr int BLOCK_K = 64;  // 64 x 2 B = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int NUM_THREADS = 256;
 constexpr int EPI_WARP0 = 4;  // epilogue warps 4..7 (warp_idx % 4 selects the TMEM lane quarter)
+constexpr int COPY_ROWS = 8;   // rows per all-gather copy piece
 constexpr int GROUP_M = 8;    // L2-friendly raster: 8 m-blocks share one sweep over n
 
 enum EpiMode : int { EPI_NONE = 0, EPI_GELU_TANH = 1, EPI_GELU_ERF = 2, EPI_DGELU_TANH = 3, EPI_DGELU_ERF = 4 };
@@ -95,7 +96,8 @@ struct Cfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
   static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (power of two >= 32)
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int EPI_STAGE_BYTES = 4 * 32 * 256;  // per epilogue warp: 32 rows x 256 B, for coalesced stores
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 __device__ __forceinline__ void tile_coords(int t, const GemmParams& p, int& b, int& m_blk, int& n_blk) {
@@ -208,7 +210,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint8_t* epi_stage = smem + C::STAGES * C::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_stage + C::EPI_STAGE_BYTES);
   uint64_t* full_bar = bars;                   // [STAGES]  TMA -> MMA
   uint64_t* empty_bar = bars + C::STAGES;      // [STAGES]  MMA -> TMA
   uint64_t* tfull_bar = bars + 2 * C::STAGES;  // [2]       MMA -> epilogue
@@ -243,53 +246,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   const uint32_t tmem_base = *tmem_slot;
 
   const int total_tiles = p.batch * p.num_m * p.num_n;
-  const int n_comm = (p.comm.mode == COMM_AG) ? p.comm.comm_ctas : 0;
-  const int tile0 = (int)blockIdx.x - n_comm;          // first tile of this CTA (negative: a copy CTA)
-  const int tstride = (int)gridDim.x - n_comm;
+  const int tile0 = (int)blockIdx.x;
+  const int tstride = (int)gridDim.x;
 
-  if (tile0 < 0) {
-    // ===================================================================== all-gather copy CTA
-    // Pull the peers' shards over NVLink with 16-byte loads, block of 128 rows by block, ring order.
-    const CommParams& c = p.comm;
-    const int mpr = c.rows_per_rank / BLOCK_M;
-    const long long blk_bytes = (long long)BLOCK_M * c.row_bytes;
-    for (int ci = 1; ci < c.nranks; ++ci) {
-      const int src = (c.rank + ci) % c.nranks;
-      if (threadIdx.x == 0) spin_until_ge(&c.ready_flags[src], c.epoch, true);
-      __syncthreads();
-      for (int sb = blockIdx.x; sb < mpr; sb += n_comm) {
-        const long long off = ((long long)src * mpr + sb) * blk_bytes;
-        const uint4* from = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(c.peer_src[src]) + off);
-        uint4* to = reinterpret_cast<uint4*>(reinterpret_cast<char*>(c.local_buf) + off);
-        const long long nvec = blk_bytes >> 4;
-        for (long long i = threadIdx.x; i < nvec; i += 4 * NUM_THREADS) {
-          uint4 v0, v1, v2, v3;
-          const long long i1 = i + NUM_THREADS, i2 = i + 2 * NUM_THREADS, i3 = i + 3 * NUM_THREADS;
-          v0 = from[i];
-          if (i1 < nvec) v1 = from[i1];
-          if (i2 < nvec) v2 = from[i2];
-          if (i3 < nvec) v3 = from[i3];
-          to[i] = v0;
-          if (i1 < nvec) to[i1] = v1;
-          if (i2 < nvec) to[i2] = v2;
-          if (i3 < nvec) to[i3] = v3;
-        }
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0) st_release_gpu(&c.blk_flags[src * mpr + sb], c.epoch);
-      }
-      // tell `src` that this GPU no longer reads its shard once every copy CTA is through
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        const uint32_t old = atomicAdd(&c.counters[src], 1u);
-        if (old == (uint32_t)n_comm - 1u) {
-          c.counters[src] = 0;
-          __threadfence_system();
-          st_release_sys(&c.peer_done[src][c.rank], c.epoch);
-        }
-      }
-    }
-  } else if (warp == 0) {
+  if (warp == 0) {
     // ===================================================================== TMA producer
     if (lane == 0) {
       int stage = 0;
@@ -302,7 +262,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         if (p.comm.mode == COMM_AG && m0 / p.comm.rows_per_rank != p.comm.rank) {
           // rows of a remote shard: wait until a copy CTA has landed this 128-row block, then make the
           // generic-proxy writes visible to the TMA (async proxy) reads that follow
-          spin_until_ge(&p.comm.blk_flags[m_blk], p.comm.epoch, false);
+          spin_until_ge(&p.comm.blk_flags[m_blk], (uint32_t)(BLOCK_M / COPY_ROWS), false);
           asm volatile("fence.proxy.async;" ::: "memory");
         }
         for (int kb = 0; kb < p.num_k; ++kb) {
@@ -374,7 +334,57 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         }
       }
     }
-  } else if (warp >= EPI_WARP0) {
+  } else if (warp < EPI_WARP0) {
+    // ===================================================================== all-gather copy warps (2, 3)
+    // Every CTA's two spare warps pull 8-row pieces of the peers' shards over NVLink (16-byte peer loads,
+    // 16 in flight per lane) into the local gathered buffer, ring order, and count each piece into its
+    // 128-row block's arrival counter; the TMA producer of whichever CTA needs that block waits on it.
+    if (p.comm.mode == COMM_AG) {
+      const CommParams& c = p.comm;
+      const long long piece_bytes = (long long)COPY_ROWS * c.row_bytes;
+      const int pieces_per_rank = c.rows_per_rank / COPY_ROWS;
+      const int total_pieces = (c.nranks - 1) * pieces_per_rank;
+      const int wid = (int)blockIdx.x * 2 + (warp - 2), wstride = (int)gridDim.x * 2;
+      int waited_src = -1;
+      for (int pc = wid; pc < total_pieces; pc += wstride) {
+        const int ci = pc / pieces_per_rank + 1, within = pc % pieces_per_rank;
+        const int src = (c.rank + ci) % c.nranks;
+        if (src != waited_src) {
+          if (lane == 0) spin_until_ge(&c.ready_flags[src], c.epoch, true);
+          __syncwarp();
+          waited_src = src;
+        }
+        const long long off = ((long long)src * pieces_per_rank + within) * piece_bytes;
+        const uint4* from = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(c.peer_src[src]) + off);
+        uint4* to = reinterpret_cast<uint4*>(reinterpret_cast<char*>(c.local_buf) + off);
+        const int nvec = (int)(piece_bytes >> 4);
+        constexpr int U = 16;
+        for (int i = lane; i < nvec; i += U * 32) {
+          uint4 v[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+            if (i + u * 32 < nvec) v[u] = from[i + u * 32];
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+            if (i + u * 32 < nvec) to[i + u * 32] = v[u];
+        }
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) atomicAdd(&c.blk_flags[(src * pieces_per_rank + within) / (BLOCK_M / COPY_ROWS)], 1u);
+      }
+      // when every copy warp of the grid is through, release the peers' shards for their next write
+      __syncwarp();
+      if (lane == 0) {
+        const uint32_t old = atomicAdd(&c.counters[0], 1u);
+        if (old == (uint32_t)wstride - 1u) {
+          c.counters[0] = 0;
+          __threadfence_system();
+          for (int j = 0; j < c.nranks; ++j)
+            if (j != c.rank) st_release_sys(&c.peer_done[j][c.rank], c.epoch);
+        }
+      }
+    }
+  } else {
     // ===================================================================== epilogue
     const int ew = warp - EPI_WARP0;  // == warp % 4: TMEM lanes [32*ew, 32*ew+32)
     int acc = 0;
@@ -404,6 +414,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         c_base = reinterpret_cast<char*>(p.comm.peer_stage[dest]);
         row_in_c = (long long)p.comm.rank * p.comm.rows_per_rank + (row - (long long)dest * p.comm.rows_per_rank);
       }
+      // whole tile in range and a 16-bit output: stage through shared memory for coalesced row stores
+      const bool staged = p.comm.mode == COMM_RS && out_es == 2 && c_vec_ok && (m_blk * BLOCK_M + BLOCK_M <= p.M) && (n0 + BN <= p.N);
+      uint8_t* wstage = epi_stage + ew * (32 * 256);
+      const long long row_in_c0 = row_in_c - lane;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t(ew * 32) << 16) + acc * BN;
@@ -451,7 +465,43 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
               for (int i = 0; i < 32; ++i) v[i] = smpk::gelu_erf(v[i]);
             }
           }
-          store32_dyn(c_base, p.out_dtype, coff, v, full && c_vec_ok, nvalid);
+          if (staged) {
+            // 32 fp32 -> 32 x 16 bit = 4 x 16 B, written to this warp's staging rows with an XOR swizzle
+            uint4 pk[4];
+            if (p.out_dtype == SMPK_BF16) {
+              __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+              for (int i = 0; i < 16; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+            } else {
+              __half2* h = reinterpret_cast<__half2*>(pk);
+#pragma unroll
+              for (int i = 0; i < 16; ++i) h[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int u = ((c & 3) * 4 + j) ^ (lane & 15);
+              *reinterpret_cast<uint4*>(wstage + lane * 256 + u * 16) = pk[j];
+            }
+          } else {
+            store32_dyn(c_base, p.out_dtype, coff, v, full && c_vec_ok, nvalid);
+          }
+        }
+        if (staged && ((c & 3) == 3 || c == BN / 32 - 1)) {
+          // flush up to 128 columns: each row's bytes leave as one contiguous run (coalesced / NVLink friendly)
+          constexpr int PASS_COLS = BN < 128 ? BN : 128;
+          constexpr int UPR = PASS_COLS * 2 / 16;            // 16-byte units per row
+          constexpr int RPI = 32 / UPR;                      // rows per store instruction
+          __syncwarp();
+          const int pass_col0 = n0 + (c / 4) * 128;
+          const int u = lane % UPR;
+#pragma unroll
+          for (int ps = 0; ps < 32 / RPI; ++ps) {
+            const int rr = ps * RPI + lane / UPR;
+            const uint4 val = *reinterpret_cast<const uint4*>(wstage + rr * 256 + ((u ^ (rr & 15)) * 16));
+            const long long off = (long long)b * p.c_bs + (row_in_c0 + rr) * p.ldc + pass_col0;
+            *reinterpret_cast<uint4*>(c_base + off * 2 + u * 16) = val;
+          }
+          __syncwarp();
         }
       }
       if (p.comm.mode == COMM_RS) {
@@ -556,14 +606,10 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStre
   const int total = p.batch * p.num_m * p.num_n;
   int grid = smpk::num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (total < grid) grid = total;
   if (p.comm.mode == COMM_AG) {
-    // copy CTAs + GEMM CTAs must all be co-resident (the GEMM CTAs wait on flags the copy CTAs raise)
-    int gemm_ctas = grid - p.comm.comm_ctas;
-    if (gemm_ctas < 1) return smpk::set_error("gemm_comm: comm_ctas=%d leaves no CTA for the GEMM", p.comm.comm_ctas);
-    if (total < gemm_ctas) gemm_ctas = total;
-    grid = gemm_ctas + p.comm.comm_ctas;
-  } else if (total < grid) {
-    grid = total;
+    // arrival counters of the row blocks start at zero for this launch
+    SMPK_CHECK_CUDA(cudaMemsetAsync(p.comm.blk_flags, 0, sizeof(uint32_t) * (size_t)p.num_m, stream));
   }
   gemm_tcgen05_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
   SMPK_CHECK_CUDA(cudaGetLastError());
@@ -613,8 +659,7 @@ SMPK_API int smpk_gemm_comm(void* stream, int in_dtype, int out_dtype, int M, in
                "gemm_comm: M=%d must be nranks x rows_per_rank with rows_per_rank %% 128 == 0 (got %d x %d)", M,
                comm->nranks, comm->rows_per_rank);
   SMPK_REQUIRE(comm->mode != COMM_RS || aux == nullptr, "gemm_comm: aux output is not supported with reduce-scatter");
-  SMPK_REQUIRE(comm->mode != COMM_AG || (comm->comm_ctas >= 1 && !a_mn_major),
-               "gemm_comm: all-gather mode needs comm_ctas >= 1 and a K-major A operand");
+  SMPK_REQUIRE(comm->mode != COMM_AG || !a_mn_major, "gemm_comm: all-gather mode needs a K-major A operand");
   return gemm_impl(stream, in_dtype, out_dtype, M, N, K, 1, A, lda, 0, a_mn_major, B, ldb, 0, b_mn_major, C, ldc, 0, bias,
                    bias_dtype, R, ldr, 0, r_dtype, aux, alpha, beta, epi, max_ctas, comm);
 }

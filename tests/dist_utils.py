@@ -45,10 +45,12 @@ def _from_wire(obj):
     return obj
 
 
-def _entry(rank, world, port, fn, args, queue):
+def _entry(rank, world, port, fn, args, queue, use_cuda=False):
     os.environ.update({"RANK": str(rank), "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank),
                        "LOCAL_WORLD_SIZE": str(world), "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port),
-                       "SMP_LOG_LEVEL": os.environ.get("SMP_LOG_LEVEL", "warning"), "CUDA_VISIBLE_DEVICES": ""})
+                       "SMP_LOG_LEVEL": os.environ.get("SMP_LOG_LEVEL", "warning")})
+    if not use_cuda:
+        os.environ["CUDA_VISIBLE_DEVICES"] = ""
     sys.path.insert(0, ROOT)
     try:
         out = _to_wire(fn(rank, world, *args))
@@ -58,11 +60,11 @@ def _entry(rank, world, port, fn, args, queue):
         raise
 
 
-def run_distributed(fn, world, *args, timeout=240):
+def run_distributed(fn, world, *args, timeout=240, use_cuda=False):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, q)) for r in range(world)]
+    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, q, use_cuda)) for r in range(world)]
     for p in procs:
         p.start()
     results = {}
