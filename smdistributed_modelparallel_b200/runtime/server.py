@@ -268,6 +268,12 @@ class ExecutionServer:
             self._done_msg = msg
         elif isinstance(msg, tuple) and msg and msg[0] == "partition":
             pass
+        elif isinstance(msg, tuple) and msg and msg[0] == "mb_done":
+            # the leader finished this microbatch's backward: its graphs can go
+            mb = msg[1]
+            for cid in [c for c, r in self.records.items() if r.mb == mb]:
+                del self.records[cid]
+            self.boundaries.pop(mb, None)
         else:
             raise SMPRuntimeError(f"unexpected pipeline message {type(msg).__name__}")
 
@@ -442,6 +448,10 @@ class ExecutionServer:
                 tensors, grads = self.deferred_bwd.pop(mb)
                 self._backward_segment(mb, tensors, grads)
                 self.boundaries.pop(mb, None)
+                del tensors, grads
+                for r in self.core.get_pp_group():
+                    if r != self.me:
+                        self.comm.server_send(("mb_done", mb), r)
                 pipe.mark_done(mb)
                 self.core.timeline_record_pipeline_event(mb, "bwd_end")
             st.microbatch = prev
