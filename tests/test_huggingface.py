@@ -1,0 +1,120 @@
+"""HuggingFace module replacement + state-dict translation (reference test tier: test/torch/mp/huggingface/*,
+SURVEY 4).  A tiny HF model is built under smp.tensor_parallelism, replaced by the distributed transformer,
+loaded with translated weights and compared with the original HF forward on CPU (tp=1, fp32)."""
+
+import pytest
+import torch
+
+transformers = pytest.importorskip("transformers")
+
+import smdistributed_modelparallel_b200 as smp
+
+
+def _lm_case(cfg, cls):
+    smp.reset()
+    smp.init({"microbatches": 1})
+    torch.manual_seed(0)
+    hf = cls(cfg).eval()
+    hf_sd = {k: v.clone() for k, v in hf.state_dict().items()}
+    ids = torch.randint(0, cfg.vocab_size, (2, 16))
+    with torch.no_grad():
+        ref = hf(input_ids=ids, labels=ids)
+    with smp.tensor_parallelism(enabled=True):
+        hf2 = cls(cfg)
+    model = smp.DistributedModel(hf2)
+    assert type(model.module).__name__ == "DistributedTransformerLMHead"
+    to_hf, to_smp = smp.state.tp_registry.active_translate_functions[0]
+    model.load_state_dict(to_smp(hf_sd), strict=False)
+    model.eval()
+
+    @smp.step
+    def fwd(model, ids):
+        out = model(input_ids=ids, labels=ids)
+        return out.loss, out.logits
+
+    with torch.no_grad():
+        loss, logits = fwd(model, ids)
+    assert abs(loss.reduce_mean().item() - ref.loss.item()) < 1e-5
+    assert (logits.concat() - ref.logits).abs().max().item() < 1e-5
+    back = to_hf(model.state_dict())
+    for k, v in hf_sd.items():
+        assert k in back, k
+        assert torch.equal(back[k].to(v.dtype), v), k
+
+
+def test_gpt2_replacement_matches_hf():
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    _lm_case(GPT2Config(n_layer=2, n_head=4, n_embd=32, n_positions=32, vocab_size=96, resid_pdrop=0, embd_pdrop=0,
+                        attn_pdrop=0), GPT2LMHeadModel)
+
+
+def test_gptj_replacement_matches_hf():
+    from transformers import GPTJConfig, GPTJForCausalLM
+
+    _lm_case(GPTJConfig(n_layer=2, n_head=4, n_embd=32, n_positions=32, vocab_size=96, rotary_dim=4, resid_pdrop=0,
+                        embd_pdrop=0, attn_pdrop=0), GPTJForCausalLM)
+
+
+def test_gptneox_replacement_matches_hf():
+    from transformers import GPTNeoXConfig, GPTNeoXForCausalLM
+
+    _lm_case(GPTNeoXConfig(num_hidden_layers=2, num_attention_heads=4, hidden_size=32, intermediate_size=64,
+                           max_position_embeddings=32, vocab_size=96, rotary_pct=0.5, hidden_dropout=0.0,
+                           attention_dropout=0.0), GPTNeoXForCausalLM)
+
+
+def test_gptneo_replacement_matches_hf():
+    from transformers import GPTNeoConfig, GPTNeoForCausalLM
+
+    cfg = GPTNeoConfig(num_layers=2, num_heads=4, hidden_size=32, max_position_embeddings=32, vocab_size=96,
+                       attention_types=[[["global"], 2]], resid_dropout=0, embed_dropout=0, attention_dropout=0)
+    _lm_case(cfg, GPTNeoForCausalLM)
+
+
+def test_bert_encoder_replacement_matches_hf():
+    from transformers import BertConfig, BertModel
+
+    smp.reset()
+    smp.init({"microbatches": 1})
+    torch.manual_seed(0)
+    cfg = BertConfig(num_hidden_layers=2, num_attention_heads=4, hidden_size=32, intermediate_size=64, vocab_size=96,
+                     max_position_embeddings=32, hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    hf = BertModel(cfg).eval()
+    hf_sd = {k: v.clone() for k, v in hf.state_dict().items()}
+    ids = torch.randint(0, cfg.vocab_size, (2, 16))
+    with torch.no_grad():
+        ref = hf(input_ids=ids).last_hidden_state
+    with smp.tensor_parallelism(enabled=True):
+        hf2 = BertModel(cfg)
+    model = smp.DistributedModel(hf2)
+    assert type(model.module.encoder).__name__ == "DistributedTransformer"
+    to_hf, _ = smp.state.tp_registry.active_translate_functions[0]
+    # a full HF state dict is translated on load; the submodule prefix ("encoder.") is carried through
+    assert any("encoder.seq_layers.0.attention.query.weight" in k for k in model.state_dict())
+    model.load_state_dict(hf_sd)
+    model.eval()
+
+    @smp.step
+    def fwd(model, ids):
+        return model(input_ids=ids).last_hidden_state
+
+    with torch.no_grad():
+        out = fwd(model, ids).concat()
+    assert (out - ref).abs().max().item() < 1e-5
+    back = to_hf(model.state_dict())
+    for k, v in hf_sd.items():
+        assert k in back and torch.equal(back[k], v), k
+
+
+def test_unsupported_config_falls_back():
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    smp.reset()
+    smp.init({"microbatches": 1})
+    cfg = GPT2Config(n_layer=1, n_head=2, n_embd=16, n_positions=16, vocab_size=32, reorder_and_upcast_attn=True)
+    with smp.tensor_parallelism(enabled=True):
+        hf = GPT2LMHeadModel(cfg)
+    model = smp.DistributedModel(hf)
+    # the LM-head mapping declines this config; the per-layer / Linear / Embedding mappings may still apply
+    assert type(model.module).__name__ != "DistributedTransformerLMHead"
