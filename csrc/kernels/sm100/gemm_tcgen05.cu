@@ -45,7 +45,12 @@ enum EpiMode : int { EPI_NONE = 0, EPI_GELU_TANH = 1, EPI_GELU_ERF = 2, EPI_DGEL
 //            the staging slot of the rank that owns those rows (P2P stores), remote destinations first,
 //            and raises that rank's arrival flag once all tiles for it are written; a small reduce
 //            kernel on the owner sums the slots.
-enum CommMode : int { COMM_NONE = 0, COMM_AG = 1, COMM_RS = 2 };
+//   COMM_AGB: the B operand (a weight) is the first tensor of a sharded-data-parallel unit whose flat buffer is
+//            striped over the ranks in 8-row pieces (piece g lives on rank g % n at index g / n).  The copy
+//            warps gather the WHOLE unit into `local_buf` (the weight first), counting pieces per BN-row
+//            block; the TMA producer waits for the n-block it is about to load.  This is the ZeRO-3
+//            parameter all-gather fused into the first GEMM that consumes the unit.
+enum CommMode : int { COMM_NONE = 0, COMM_AG = 1, COMM_RS = 2, COMM_AGB = 3 };
 constexpr int MAX_RANKS = 8;
 
 struct CommParams {
@@ -55,6 +60,7 @@ struct CommParams {
   const void* peer_src[MAX_RANKS];     // peer j's gathered buffer (same layout as mine); I read its slot j
   void* local_buf;                     // my gathered buffer [nranks * rows_per_rank, K]
   long long row_bytes;                 // K * 2
+  long long total_rows;                // COMM_AGB: rows of the whole unit (nranks * rows_per_rank)
   uint32_t* blk_flags;                 // local [M / 128]: block landed (== epoch)
   const uint32_t* ready_flags;         // local [nranks]: peer j's slot is final for this epoch (written by j)
   uint32_t* peer_done[MAX_RANKS];      // peer j's done[nranks]; I set [rank] = epoch after copying its slot
@@ -137,7 +143,7 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t v, boo
 // RS finishes with the local shard (remote tiles leave first).
 __device__ __forceinline__ int permute_m_block(int m_blk, const GemmParams& p) {
   const CommParams& c = p.comm;
-  if (c.mode == COMM_NONE) return m_blk;
+  if (c.mode != COMM_AG && c.mode != COMM_RS) return m_blk;
   const int mpr = c.rows_per_rank / BLOCK_M;
   const int ci = m_blk / mpr, within = m_blk - ci * mpr;
   const int chunk = (c.mode == COMM_AG) ? (c.rank + ci) % c.nranks : (c.rank + 1 + ci) % c.nranks;
@@ -265,6 +271,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           spin_until_ge(&p.comm.blk_flags[m_blk], (uint32_t)(BLOCK_M / COPY_ROWS), false);
           asm volatile("fence.proxy.async;" ::: "memory");
         }
+        if (p.comm.mode == COMM_AGB) {
+          // weight rows of this n-block are being gathered by the copy warps (all CTAs); pieces are 8 rows
+          const long long hi = min((long long)n0 + BN, p.comm.total_rows);
+          spin_until_ge(&p.comm.blk_flags[n_blk], (uint32_t)((hi - n0) / COPY_ROWS), false);
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         for (int kb = 0; kb < p.num_k; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
@@ -382,6 +394,39 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           for (int j = 0; j < c.nranks; ++j)
             if (j != c.rank) st_release_sys(&c.peer_done[j][c.rank], c.epoch);
         }
+      }
+    }
+    if (p.comm.mode == COMM_AGB) {
+      const CommParams& c = p.comm;
+      const long long piece_bytes = (long long)COPY_ROWS * c.row_bytes;
+      const long long total_pieces = c.total_rows / COPY_ROWS;
+      const int wid = (int)blockIdx.x * 2 + (warp - 2), wstride = (int)gridDim.x * 2;
+      uint32_t waited = 1u << c.rank;
+      for (long long pc = wid; pc < total_pieces; pc += wstride) {
+        const long long q = pc / c.nranks;
+        const int src = (c.rank + (int)(pc % c.nranks)) % c.nranks;
+        if (!((waited >> src) & 1u)) {
+          if (lane == 0) spin_until_ge(&c.ready_flags[src], c.epoch, true);
+          __syncwarp();
+          waited |= 1u << src;
+        }
+        const long long g = q * c.nranks + src;
+        const uint4* from = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(c.peer_src[src]) + q * piece_bytes);
+        uint4* to = reinterpret_cast<uint4*>(reinterpret_cast<char*>(c.local_buf) + g * piece_bytes);
+        const int nvec = (int)(piece_bytes >> 4);
+        constexpr int U = 16;
+        for (int i = lane; i < nvec; i += U * 32) {
+          uint4 v[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+            if (i + u * 32 < nvec) v[u] = from[i + u * 32];
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+            if (i + u * 32 < nvec) to[i + u * 32] = v[u];
+        }
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) atomicAdd(&c.blk_flags[(g * COPY_ROWS) / BN], 1u);
       }
     }
   } else {
@@ -611,6 +656,13 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStre
     // arrival counters of the row blocks start at zero for this launch
     SMPK_CHECK_CUDA(cudaMemsetAsync(p.comm.blk_flags, 0, sizeof(uint32_t) * (size_t)p.num_m, stream));
   }
+  if (p.comm.mode == COMM_AGB) {
+    // the copy warps of EVERY resident CTA gather the unit, so the grid is never cut below the SM count
+    grid = smpk::num_sms();
+    if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+    const size_t nblk = (size_t)((p.comm.total_rows + BN - 1) / BN);
+    SMPK_CHECK_CUDA(cudaMemsetAsync(p.comm.blk_flags, 0, sizeof(uint32_t) * nblk, stream));
+  }
   gemm_tcgen05_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
   SMPK_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -653,11 +705,20 @@ SMPK_API int smpk_gemm_comm(void* stream, int in_dtype, int out_dtype, int M, in
                             int a_mn_major, const void* B, int ldb, int b_mn_major, void* C, int ldc,
                             const void* bias, int bias_dtype, const void* R, int ldr, int r_dtype, float beta,
                             void* aux, float alpha, int epi, int max_ctas, const SmpkCommDesc* comm) {
-  SMPK_REQUIRE(comm != nullptr && (comm->mode == COMM_AG || comm->mode == COMM_RS), "gemm_comm: bad comm descriptor");
+  SMPK_REQUIRE(comm != nullptr && (comm->mode == COMM_AG || comm->mode == COMM_RS || comm->mode == COMM_AGB),
+               "gemm_comm: bad comm descriptor");
   SMPK_REQUIRE(comm->nranks >= 2 && comm->nranks <= MAX_RANKS, "gemm_comm: nranks %d out of range", comm->nranks);
-  SMPK_REQUIRE(comm->rows_per_rank % BLOCK_M == 0 && comm->rows_per_rank * comm->nranks == M,
-               "gemm_comm: M=%d must be nranks x rows_per_rank with rows_per_rank %% 128 == 0 (got %d x %d)", M,
-               comm->nranks, comm->rows_per_rank);
+  if (comm->mode == COMM_AGB) {
+    SMPK_REQUIRE(!b_mn_major && ldb == K && B == comm->local_buf,
+                 "gemm_comm: gathered-weight mode needs a dense K-major B at the start of the unit buffer");
+    SMPK_REQUIRE(comm->rows_per_rank % COPY_ROWS == 0 && (long long)comm->rows_per_rank * comm->nranks >= N,
+                 "gemm_comm: unit of %d x %d rows does not cover the %d weight rows", comm->nranks,
+                 comm->rows_per_rank, N);
+  } else {
+    SMPK_REQUIRE(comm->rows_per_rank % BLOCK_M == 0 && comm->rows_per_rank * comm->nranks == M,
+                 "gemm_comm: M=%d must be nranks x rows_per_rank with rows_per_rank %% 128 == 0 (got %d x %d)", M,
+                 comm->nranks, comm->rows_per_rank);
+  }
   SMPK_REQUIRE(comm->mode != COMM_RS || aux == nullptr, "gemm_comm: aux output is not supported with reduce-scatter");
   SMPK_REQUIRE(comm->mode != COMM_AG || !a_mn_major, "gemm_comm: all-gather mode needs a K-major A operand");
   return gemm_impl(stream, in_dtype, out_dtype, M, N, K, 1, A, lda, 0, a_mn_major, B, ldb, 0, b_mn_major, C, ldc, 0, bias,
@@ -695,6 +756,7 @@ static int gemm_impl(void* stream, int in_dtype, int out_dtype, int M, int N, in
     c.mode = comm->mode; c.nranks = comm->nranks; c.rank = comm->rank; c.rows_per_rank = comm->rows_per_rank;
     c.comm_ctas = comm->comm_ctas; c.epoch = comm->epoch;
     c.local_buf = comm->local_buf; c.row_bytes = (long long)K * 2;
+    c.total_rows = (long long)comm->rows_per_rank * comm->nranks;
     c.blk_flags = comm->blk_flags; c.ready_flags = comm->ready_flags; c.counters = comm->counters;
     for (int i = 0; i < MAX_RANKS; ++i) {
       c.peer_src[i] = comm->peer_src[i]; c.peer_done[i] = comm->peer_done[i];

@@ -66,6 +66,20 @@ int smpk_flags_wait(void* stream, const void* flags, int n, int skip, unsigned i
 int smpk_p2p_allgather(void* stream, void* const* peer_src, void* local_buf, long long slot_bytes,
                        const void* ready_flags, void* const* peer_done, void* counters, int nranks, int rank,
                        unsigned int epoch, int ctas);
+/* Sharded-data-parallel unit kernels (csrc/kernels/sm100/sdp_comm.cu).  A unit's flat buffer is striped over the
+ * ranks in fixed pieces: piece g lives on rank g % n at piece index g / n.  smpk_sdp_gather pulls every piece from
+ * its owner's shard by peer loads into `full`; smpk_gemm_comm mode 3 does the same from inside the first GEMM that
+ * consumes the unit (B == full, rows_per_rank = shard rows of K elements, 8-row pieces).  smpk_sdp_reduce_adam sums
+ * the ranks' fp32 gradient buffers for this rank's pieces (reduce-scatter by peer loads), scales, accumulates into
+ * grad_shard (mode 0) or applies Adam/AdamW to master/exp_avg/exp_avg_sq and writes the low-precision shard (mode 1).
+ * Engine delegated to DeepSpeed in the reference (torch/optimizers/optimizer.py:46-49,471-491). */
+int smpk_sdp_gather(void* stream, void* const* peer_shard, void* full, long long piece_bytes, long long pieces_per_rank,
+                    const void* ready, unsigned int epoch, int nranks, int rank, int ctas);
+int smpk_sdp_reduce_adam(void* stream, void* const* peer_grad, float* grad_shard, float* master, float* exp_avg,
+                         float* exp_avg_sq, void* lowp, int lowp_dtype, long long piece_elems, long long pieces_per_rank,
+                         const void* ready, void* const* peer_consumed, void* counter, unsigned int epoch, int nranks,
+                         int rank, float scale, float beta, int mode, float lr, float beta1, float beta2, float eps,
+                         float wd, int step, int adamw, int bias_correction, float grad_scale, int ctas);
 int smpk_rs_reduce(void* stream, const void* staging, const void* arrived, void* const* peer_reduced, void* counter,
                    const void* residual, int res_dtype, const void* bias, int bias_dtype, void* out, int out_dtype,
                    long long rows, int N, int nranks, int rank, int dtype, unsigned int epoch);

@@ -260,6 +260,8 @@ class DistributedModel(nn.Module):
         sync = (self._backward_passes % self.backward_passes_per_step) == 0
         if self.reducer is not None:
             self.reducer.require_sync = sync
+        if self.sdp_engine is not None:
+            self.sdp_engine._sync_step = sync
         ran_backward = {"v": False}
         self._ran_backward = ran_backward
         try:

@@ -193,6 +193,11 @@ class DistributedAttentionLayer(DistributedModule):
                 bound = 1.0 / math.sqrt(self.num_attention_heads * self.attention_head_size)
                 nn.init.uniform_(self.dense_bias, -bound, bound)
 
+    def sdp_first_weight(self):
+        """The weight this module's forward multiplies first (sharded data parallelism gathers the unit from
+        inside that GEMM)."""
+        return self.qkv_weight
+
     # ---- pieces (also used by DistributedTransformerLayer for the parallel attention+MLP form)
     def attention_core(self, qkv, B, S, attention_mask):
         """qkv [T, 3*local] for all T = B*S tokens of the tp group's batch -> context [T, local]."""
@@ -349,6 +354,9 @@ class DistributedTransformerOutputLayer(DistributedModule):
         return {"dense1.weight": (0, sz), "dense1.bias": (0, sz), "dense2.weight": (1, sz),
                 "dense2.bias": ("one_rank", None)}
 
+    def sdp_first_weight(self):
+        return self.dense1_weight
+
     def _act_other(self, h):
         return F.relu(h) if self.activation == "relu" else getattr(F, self.activation)(h)
 
@@ -419,6 +427,9 @@ class DistributedTransformerLayer(DistributedModule):
         if self.add_cross_attention:
             return hidden, attention_mask, cross_states, cross_mask
         return hidden, attention_mask
+
+    def sdp_first_weight(self):
+        return self.attention.qkv_weight
 
     def _parallel_forward(self, hidden, attention_mask):
         """x + attn(ln_a(x)) + mlp(ln_m(x)).  The attention-dense partial product rides into the MLP's

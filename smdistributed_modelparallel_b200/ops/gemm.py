@@ -24,6 +24,9 @@ _EPI_BY_NAME = {"none": EPI_NONE, "gelu_tanh": EPI_GELU_TANH, "gelu_erf": EPI_GE
 # diagnostics: how many GEMMs ran natively / fell back to torch.matmul (shape or alignment limits)
 stats = {"native": 0, "fallback": 0}
 
+# gathers deferred to the GEMM that first reads a sharded unit's weight (parallel/sdp_fused.py)
+from ._sdp_hook import pending_gathers as _sdp_pending  # noqa: E402
+
 # optional cap on the persistent grid (leaves SMs free for kernels on side streams)
 _max_ctas = 0
 
@@ -108,6 +111,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
         out_dtype = out.dtype if out is not None else a.dtype
     out_shape = (batch, M, Nn) if a.dim() == 3 else (M, Nn)
 
+    gather = _sdp_pending.get(b.data_ptr()) if _sdp_pending else None
+    if gather is not None and (a.dim() != 2 or b_mn_major or b.stride(0) != K or not _native_ok(a, b, out, residual, bias)):
+        gather(None)                 # cannot fuse into this GEMM: gather the unit now, stand-alone
+        gather = None
     if not _native_ok(a, b, out, residual, bias):
         if a.is_cuda:
             stats["fallback"] += 1
@@ -128,6 +135,19 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
 
     stats["native"] += 1
     N.count_launch()
+    if gather is not None:
+        # B is the first weight of a sharded-data-parallel unit: this GEMM's copy warps all-gather the whole
+        # unit from the peers' shards while its MMA warps consume weight rows as they land
+        import ctypes
+        desc = gather((M, Nn, K))
+        N.call("smpk_gemm_comm", N.stream_ptr(a.device), N.dtype_code(a.dtype), N.dtype_code(out_dtype), M, Nn, K,
+               a.data_ptr(), a.stride(-2), int(a_mn_major), b.data_ptr(), b.stride(-2), 0, out.data_ptr(),
+               out.stride(-2), N.ptr(bias), N.dtype_code(bias.dtype) if bias is not None else 0, N.ptr(residual),
+               residual.stride(-2) if residual is not None else 0,
+               N.dtype_code(residual.dtype) if residual is not None else 0, float(beta), N.ptr(aux_out), float(alpha),
+               epi, _max_ctas, ctypes.byref(desc))
+        stats["sdp_fused_gather"] = stats.get("sdp_fused_gather", 0) + 1
+        return out
     N.call(
         "smpk_gemm", N.stream_ptr(a.device), N.dtype_code(a.dtype), N.dtype_code(out_dtype), M, Nn, K, batch,
         a.data_ptr(), a.stride(-2), bs(a), int(a_mn_major),

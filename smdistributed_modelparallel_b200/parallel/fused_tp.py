@@ -60,7 +60,7 @@ def _ptr_array(ptrs):
 class SymmetricBuffer:
     """One allocation of ``nbytes`` on every rank of the group, with every peer's copy mapped locally."""
 
-    def __init__(self, nbytes, ranks, me_index, comm):
+    def __init__(self, nbytes, ranks, me_index, comm, pg=None):
         lib = native_core.load()
         self.nbytes = int(nbytes)
         ptr = ctypes.c_void_p()
@@ -68,7 +68,11 @@ class SymmetricBuffer:
         if lib.smpc_symm_alloc(self.nbytes, ctypes.byref(ptr), handle) != 0:
             raise RuntimeError(f"symmetric allocation failed: {lib.smpc_symm_last_error().decode()}")
         self.ptr = ptr.value
-        handles = comm.allgather(bytes(handle.raw), CommGroup.TP_GROUP)
+        if pg is not None:                  # exchange over a torch.distributed group (sharded data parallelism)
+            handles = [None] * dist.get_world_size(pg)
+            dist.all_gather_object(handles, bytes(handle.raw), group=pg)
+        else:
+            handles = comm.allgather(bytes(handle.raw), CommGroup.TP_GROUP)
         self.peer_ptrs = []
         for j, h in enumerate(handles):
             if j == me_index:

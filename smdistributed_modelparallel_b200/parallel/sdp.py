@@ -41,23 +41,43 @@ from .grad_buffer import GradBuffer
 class Unit:
     """A set of parameters gathered / released together; stored flat and sharded."""
 
-    def __init__(self, name, module, params, gi, degree, rank, device):
-        self.name, self.module, self.params, self.gi = name, module, params, gi
+    def __init__(self, name, module, params, gi, degree, rank, device, striped=False):
+        self.name, self.module, self.gi = name, module, gi
+        self.degree, self.rank = degree, rank
+        # the weight the unit's module multiplies first goes to offset 0: the fused kernel gathers the unit
+        # from inside that GEMM (parallel/sdp_fused.py)
+        first = getattr(module, "sdp_first_weight", lambda: None)() if striped else None
+        self.first_weight = first if any(first is p for p in params) and first.dim() == 2 else None
+        if self.first_weight is not None:
+            params = [self.first_weight] + [p for p in params if p is not self.first_weight]
+        self.params = params
         self.offsets = {}
         off = 0
         for p in params:
             self.offsets[p] = off
             off = (off + p.numel() + 7) // 8 * 8
-        mult = degree * 8
-        self.numel = (off + mult - 1) // mult * mult
-        self.per = self.numel // degree
+        if striped:
+            # piece = 8 rows of the first weight (or 8 x 4096 elements); piece g lives on rank g % degree
+            self.row = self.first_weight.shape[1] if self.first_weight is not None else 4096
+            if self.row % 8:
+                self.row, self.first_weight = 4096, None
+            self.piece = 8 * self.row
+            mult = degree * self.piece
+            self.numel = (off + mult - 1) // mult * mult
+            self.per = self.numel // degree
+        else:
+            mult = degree * 8
+            self.numel = (off + mult - 1) // mult * mult
+            self.per = self.numel // degree
+            self.piece, self.row = self.per, self.per       # one piece per rank: plain contiguous sharding
+        self.ppr = self.per // self.piece                   # pieces per rank
         self.dtype = params[0].dtype
         self.shapes = {p: tuple(p.shape) for p in params}
         self.numels = {p: p.numel() for p in params}
         full = torch.zeros(self.numel, dtype=self.dtype, device=device)
         for p in params:
             full[self.offsets[p]:self.offsets[p] + p.numel()].copy_(p.data.reshape(-1))
-        self.shard = full[rank * self.per:(rank + 1) * self.per].clone()
+        self.shard = self.shard_of(full).clone()
         self.master = nn.Parameter(self.shard.float(), requires_grad=True)
         self.grad_shard = torch.zeros(self.per, dtype=torch.float32, device=device)
         self.master.grad = self.grad_shard
@@ -65,9 +85,17 @@ class Unit:
         self.full_grad = None       # fp32 [numel] while the unit's backward is in flight
         self.gather_work = None
         self.users = 0
+        self.lazy_pending = False   # gather deferred to the first GEMM reading first_weight
+        self.recompute_seen = False # forward re-run during backward (activation checkpointing)
+        self.updated = False        # Adam already applied by the fused reduce kernel this step
         for p in params:
             p.data = torch.empty(0, dtype=p.dtype, device=device)
             p._smp_sdp_unit = self
+
+    def shard_of(self, full, rank=None):
+        """This rank's (or ``rank``'s) elements of a full-unit tensor, in shard order."""
+        r = self.rank if rank is None else rank
+        return full.view(self.ppr, self.degree, self.piece)[:, r].reshape(-1)
 
 
 class ShardedDataParallelEngine:
@@ -107,6 +135,10 @@ class ShardedDataParallelEngine:
         self._in_backward = False
         self._step = 0
         self._hooks = []
+        self._sync_step = True
+        self.fused = False           # peer-memory kernels instead of NCCL (CUDA, shard group on one node)
+        self.fabric = None
+        self._want_fused = os.environ.get("SMP_SDP_FUSED", "1") != "0"
 
     # ------------------------------------------------------------------ construction
     def _build(self, group_of=None):
@@ -114,6 +146,8 @@ class ShardedDataParallelEngine:
             return
         self._built = True
         group_of = group_of or (lambda p: 0)
+        from . import sdp_fused
+        self.fused = self._want_fused and sdp_fused.supported(self)
         sharded = {id(p) for p in self.all_params if p.numel() >= self.threshold}
         self.persistent = [p for p in self.all_params if id(p) not in sharded]
         root = self.model.module
@@ -129,7 +163,8 @@ class ShardedDataParallelEngine:
                 seen.add(id(p))
             for gi in sorted({group_of(p) for p in plist}):
                 sub = [p for p in plist if group_of(p) == gi]
-                u = Unit(f"{names[m] or 'root'}{tag}#{gi}", m, sub, gi, self.degree, self.shard_rank, self.device)
+                u = Unit(f"{names[m] or 'root'}{tag}#{gi}", m, sub, gi, self.degree, self.shard_rank, self.device,
+                         striped=self.fused)
                 self.units.append(u)
 
         def assign(m):
@@ -163,13 +198,32 @@ class ShardedDataParallelEngine:
                 for p in self.persistent:
                     dist.broadcast(p.data, src=0)
                     self.persistent_masters[p].data.copy_(p.data)
+        if self.fused and self.units:
+            self.fabric = sdp_fused.PeerFabric(self)
         total = sum(u.numel for u in self.units)
         get_logger().debug(f"sharded DP: {len(self.units)} units, {total / 1e6:.1f} M sharded + "
                            f"{sum(p.numel() for p in self.persistent) / 1e6:.2f} M persistent parameters, degree {self.degree}")
 
     # ------------------------------------------------------------------ gather / release
-    def _issue_gather(self, u: Unit):
-        if u.full is not None or u.gather_work is not None:
+    def _issue_gather(self, u: Unit, lazy_ok=False):
+        if u.full is not None or u.gather_work is not None or u.lazy_pending:
+            return
+        if self.fused:
+            fab = self.fabric
+            if lazy_ok and u.first_weight is not None:
+                # the first GEMM reading first_weight gathers the whole unit (smpk_gemm_comm mode 3)
+                full = torch.empty(u.numel, dtype=u.dtype, device=self.device)
+                fab.defer_to_gemm(u, full)
+            else:
+                cur = torch.cuda.current_stream(self.device)
+                fab.side.wait_stream(cur)
+                with torch.cuda.stream(fab.side):
+                    full = torch.empty(u.numel, dtype=u.dtype, device=self.device)
+                    fab.gather(u, full)
+                    ev = torch.cuda.Event()
+                    ev.record(fab.side)
+                u.gather_work = ev
+            u._pending_full = full
             return
         full = torch.empty(u.numel, dtype=u.dtype, device=self.device)
         if self.degree > 1:
@@ -178,21 +232,35 @@ class ShardedDataParallelEngine:
             full.copy_(u.shard)
         u._pending_full = full
 
-    def _ensure(self, u: Unit):
+    def _ensure(self, u: Unit, lazy_ok=False):
         if u.full is None:
-            self._issue_gather(u)
+            self._issue_gather(u, lazy_ok)
             if u.gather_work is not None:
-                u.gather_work.wait()
+                if self.fused:
+                    cur = torch.cuda.current_stream(self.device)
+                    cur.wait_event(u.gather_work)
+                    u._pending_full.record_stream(cur)
+                else:
+                    u.gather_work.wait()
                 u.gather_work = None
             u.full = u._pending_full
             u._pending_full = None
             for p in u.params:
                 o = u.offsets[p]
                 p.data = u.full[o:o + u.numels[p]].view(u.shapes[p])
+        elif u.lazy_pending and not lazy_ok:
+            self.fabric.cancel_deferred(u)
 
     def _release(self, u: Unit):
         if u.full is None:
             return
+        if u.lazy_pending:
+            from . import sdp_fused
+            sdp_fused.pending_gathers.pop(u.lazy_key, None)
+            u.lazy_pending = False
+            raise SMPValidationError(
+                f"sharded data parallelism: unit {u.name} was released but the GEMM expected to gather it "
+                "(sdp_first_weight) never ran; the module read other parameters first")
         for p in u.params:
             p.data = torch.empty(0, dtype=p.dtype, device=self.device)
         u.full = None
@@ -203,6 +271,8 @@ class ShardedDataParallelEngine:
         j = self._order_index[u] + direction
         if 0 <= j < len(self._order):
             nxt = self._order[j]
+            if self.fused and nxt.first_weight is not None and (direction > 0 or nxt.recompute_seen):
+                return          # gathered from inside its own first GEMM
             if nxt.full is None and nxt.numel <= self.max_live:
                 self._issue_gather(nxt)
 
@@ -210,7 +280,9 @@ class ShardedDataParallelEngine:
         for u in units:
             if not self._order_frozen and u not in self._order:
                 self._order.append(u)
-            self._ensure(u)
+            if self._in_backward:
+                u.recompute_seen = True
+            self._ensure(u, lazy_ok=True)
             u.users += 1
         self._prefetch_after(units[-1], +1)
 
@@ -219,13 +291,17 @@ class ShardedDataParallelEngine:
             u.users -= 1
             if u.users <= 0 and u.full_grad is None:
                 u.users = 0
-                self._release(u)
+                if not self._in_backward:        # a recomputed forward is followed by its backward at once
+                    self._release(u)
 
     def _pre_backward(self, units):
         for u in units:
             self._ensure(u)
             if u.full_grad is None:
-                u.full_grad = torch.zeros(u.numel, dtype=torch.float32, device=self.device)
+                if self.fused:
+                    u.full_grad = self.fabric.acquire_slot(u)
+                else:
+                    u.full_grad = torch.zeros(u.numel, dtype=torch.float32, device=self.device)
                 for p in u.params:
                     o = u.offsets[p]
                     p.main_grad = u.full_grad[o:o + u.numels[p]].view(u.shapes[p])
@@ -248,17 +324,49 @@ class ShardedDataParallelEngine:
                 p.grad = None
             if hasattr(p, "main_grad"):
                 del p.main_grad
-        while len(self._pending_reduce) >= 2:    # bound the number of full gradient buffers alive
-            self._finish_one_reduce()
-        if self.degree > 1:
-            tmp = torch.empty(u.per, dtype=torch.float32, device=self.device)
-            work = dist.reduce_scatter_tensor(tmp, u.full_grad, group=self.shard_group, async_op=True)
-            self._pending_reduce.append((work, tmp, u, u.full_grad))
+        if self.fused:
+            self.fabric.reduce(u, self._fused_adam_args(u))
         else:
-            u.grad_shard.add_(u.full_grad[:u.per])
+            while len(self._pending_reduce) >= 2:    # bound the number of full gradient buffers alive
+                self._finish_one_reduce()
+            if self.degree > 1:
+                tmp = torch.empty(u.per, dtype=torch.float32, device=self.device)
+                work = dist.reduce_scatter_tensor(tmp, u.full_grad, group=self.shard_group, async_op=True)
+                self._pending_reduce.append((work, tmp, u, u.full_grad))
+            else:
+                u.grad_shard.add_(u.full_grad[:u.per])
         u.full_grad = None
         if u.users <= 0:
             self._release(u)
+
+    def _fused_adam_args(self, u: Unit):
+        """Hyper-parameters for applying Adam inside the reduce kernel, or None when the update has to wait:
+        not the last microbatch, a global quantity is needed first (clipping, dynamic loss scale), gradients
+        still have to cross replica groups, or the optimizer is not Adam/AdamW."""
+        opt = self.optimizer
+        if opt is None or (self.clip and self.clip > 0) or self.dynamic or self.loss_scale != 1.0:
+            return None
+        if self.replica_group is not None and dist.get_world_size(self.replica_group) > 1:
+            return None
+        if type(opt).__name__ not in ("Adam", "AdamW", "FusedAdam") or os.environ.get("SMP_SDP_FUSED_ADAM", "1") == "0":
+            return None
+        if self.state.microbatch != self.state.num_microbatches() - 1 or not self._sync_step:
+            return None
+        group = opt.param_groups[u.gi]
+        if group.get("amsgrad", False) or group.get("maximize", False):
+            return None
+        st = opt.state[u.master]
+        if "exp_avg" not in st:
+            st["step"] = torch.tensor(0.0)
+            st["exp_avg"] = torch.zeros_like(u.master.data)
+            st["exp_avg_sq"] = torch.zeros_like(u.master.data)
+        st["step"] = st["step"] + 1
+        u.updated = True
+        name = type(opt).__name__
+        return {"state": st, "scale": 1.0 / self.world, "lr": group["lr"], "beta1": group["betas"][0],
+                "beta2": group["betas"][1], "eps": group["eps"], "wd": group["weight_decay"], "step": self._step + 1,
+                "adamw": name == "AdamW" or getattr(opt, "adam_w_mode", 0) == 1,
+                "bias_correction": group.get("bias_correction", True)}
 
     def _finish_one_reduce(self):
         work, tmp, u, _keep = self._pending_reduce.pop(0)
@@ -292,10 +400,14 @@ class ShardedDataParallelEngine:
         all-reduce across replica groups and the replicated (persistent) parameters' gradients."""
         while self._pending_reduce:
             self._finish_one_reduce()
+        if self.fabric is not None:
+            self.fabric.wait_reduces()
         if not sync:
             return
         scale = 1.0 / self.world
         for u in self.units:
+            if u.updated:
+                continue
             if self.replica_group is not None and dist.get_world_size(self.replica_group) > 1:
                 dist.all_reduce(u.grad_shard, group=self.replica_group)
             u.grad_shard.mul_(scale)
@@ -400,7 +512,7 @@ class ShardedDataParallelEngine:
                         group.get("bias_correction", True), group["weight_decay"], inv, coef)
                 l5 = [[], [], [], [], []]
                 for u in self.units:
-                    if u.gi != gi:
+                    if u.gi != gi or u.updated:
                         continue
                     st = opt.state[u.master]
                     if "exp_avg" not in st:
@@ -440,7 +552,23 @@ class ShardedDataParallelEngine:
                 u.shard.copy_(u.master.data)
             for p in self.persistent:
                 p.data.copy_(self.persistent_masters[p].data)
+        for u in self.units:
+            u.updated = False
+        if self.fabric is not None:
+            self.fabric.publish_params()
         return None
+
+    def _before_shard_write(self):
+        """Host-driven rewrite of the shards (checkpoint load): no peer may still be reading them."""
+        if self.fabric is not None:
+            torch.cuda.synchronize()
+            dist.barrier(group=self.shard_group)
+
+    def _after_shard_write(self):
+        if self.fabric is not None:
+            self.fabric.publish_params()
+            torch.cuda.synchronize()
+            dist.barrier(group=self.shard_group)
 
     # ------------------------------------------------------------------ state dicts / checkpoints
     def full_state_dict(self):
@@ -458,10 +586,12 @@ class ShardedDataParallelEngine:
         for u in self.units:
             self._ensure(u)
         res = self.model.module.load_state_dict(sd, strict=strict)
+        self._before_shard_write()
         for u in self.units:                         # re-shard what was loaded
-            u.shard.copy_(u.full[self.shard_rank * u.per:(self.shard_rank + 1) * u.per])
+            u.shard.copy_(u.shard_of(u.full))
             u.master.data.copy_(u.shard)
             self._release(u)
+        self._after_shard_write()
         for p in self.persistent:
             self.persistent_masters[p].data.copy_(p.data)
         return res
@@ -471,7 +601,7 @@ class ShardedDataParallelEngine:
         return {"module": {"units": {u.name: u.shard.detach().cpu() for u in self.units},
                            "persistent": {self.model.get_param_name(p): p.detach().cpu() for p in self.persistent},
                            "buffers": {n: b.detach().cpu() for n, b in self.model.module.named_buffers()}},
-                "shard_size": self.degree, "_smp_zero2d": True}
+                "shard_size": self.degree, "_smp_zero2d": True, "striped": self.fused}
 
     def optimizer_state_dict(self):
         opt = self.optimizer
@@ -481,7 +611,7 @@ class ShardedDataParallelEngine:
                                        for p, m in self.persistent_masters.items()},
                 "partition_count": self.degree, "zero_stage": 3, "dynamic_loss_scale": self.dynamic,
                 "loss_scaler": self.loss_scaler.state_dict(), "overflow": self.overflow, "_smp_zero2d": True,
-                "step": self._step}
+                "step": self._step, "striped": self.fused}
 
     def load_optimizer_state_dict(self, sd, load_sharded_optimizer_state=True):
         self.loss_scaler.load_state_dict(sd["loss_scaler"])
@@ -491,9 +621,14 @@ class ShardedDataParallelEngine:
             return
         if sd.get("partition_count") != self.degree:
             raise SMPValidationError("sharded_data_parallel_degree differs from the checkpoint's")
+        if sd.get("striped", False) != self.fused:
+            raise SMPValidationError("checkpoint shard layout (striped vs contiguous) differs from this run's; "
+                                     "convert through a full checkpoint (partial=False)")
+        self._before_shard_write()
         for u, m in zip(self.units, sd["fp32_flat_groups"]):
             u.master.data.copy_(m.to(self.device))
             u.shard.copy_(u.master.data)
+        self._after_shard_write()
         names = {self.model.get_param_name(p): p for p in self.persistent}
         for n, m in sd.get("persistent_masters", {}).items():
             if n in names:
@@ -521,7 +656,11 @@ class ShardedDataParallelEngine:
         sd = torch.load(os.path.join(path, tag, f"model_{self.shard_rank}.pt"), map_location="cpu", weights_only=False)
         if not sd.get("_smp_zero2d") or sd.get("shard_size") != self.degree:
             raise SMPValidationError("checkpoint was not written with the same sharded_data_parallel_degree")
+        if sd.get("striped", False) != self.fused:
+            raise SMPValidationError("checkpoint shard layout (striped vs contiguous) differs from this run's; "
+                                     "convert through a full checkpoint (partial=False)")
         mod = sd["module"]
+        self._before_shard_write()
         for u in self.units:
             if u.name in mod["units"]:
                 u.shard.copy_(mod["units"][u.name].to(self.device))
@@ -537,6 +676,7 @@ class ShardedDataParallelEngine:
         for n, t in mod.get("buffers", {}).items():
             if n in bufs:
                 bufs[n].copy_(t.to(bufs[n].device))
+        self._after_shard_write()
 
     def load_optimizer_checkpoint(self, path, tag, load_sharded_optimizer_state=True):
         sd = torch.load(os.path.join(path, tag, f"optimizer_{self.shard_rank}.pt"), map_location="cpu",

@@ -1,0 +1,128 @@
+"""Native host runtime (libsmpb200_core.so) through its C ABI: gradient readiness counter, bucket planner,
+timeline, and the TCP message bus between two processes (reference tier: native self-tests in
+test/backend/*.py; GradCounter checks in test/torch/mpi_hybrid/smp_test_base.py)."""
+
+import ctypes
+import json
+import os
+import tempfile
+
+import pytest
+
+from dist_utils import run_distributed
+from smdistributed_modelparallel_b200.backend import native_core
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return native_core.load()
+
+
+def _ids(*v):
+    return (ctypes.c_int * len(v))(*v), len(v)
+
+
+def test_grad_counter_lifecycle(lib):
+    h = lib.smpc_gc_create(3, 2)
+    try:
+        for mb in range(2):
+            arr, n = _ids(0, 1, 1)                      # parameter 1 is used twice per microbatch
+            assert lib.smpc_gc_increment_expected(h, mb, arr, n) == 0
+            assert lib.smpc_gc_mark_fwd_done(h, mb) == 0
+        assert lib.smpc_gc_expected(h, 0, 1) == 2 and lib.smpc_gc_expected(h, 1, 0) == 1
+        tot = (ctypes.c_int * 3)()
+        lib.smpc_gc_expected_totals(h, tot)
+        assert list(tot) == [2, 4, 0]
+        lib.smpc_gc_set_microbatch(h, 0)
+        assert lib.smpc_gc_get_microbatch(h) == 0
+        assert lib.smpc_gc_mark_grad_computed(h, 0) == 0
+        assert lib.smpc_gc_mark_grad_computed(h, 1) == 0
+        assert lib.smpc_gc_mark_grad_computed(h, 1) == 0
+        assert lib.smpc_gc_mark_grad_computed(h, 1) == -2   # more contributions than announced
+        assert lib.smpc_gc_is_ready(h, 0) == 0
+        lib.smpc_gc_set_microbatch(h, 1)
+        assert lib.smpc_gc_mark_grad_computed(h, 0) == 1     # final contribution of the step
+        assert lib.smpc_gc_mark_grad_computed(h, 1) == 0
+        assert lib.smpc_gc_mark_grad_computed(h, 1) == 1
+        assert lib.smpc_gc_is_ready(h, 0) == 1 and lib.smpc_gc_is_ready(h, 1) == 1
+        assert lib.smpc_gc_seen(h, 1, 1) == 2
+        assert lib.smpc_gc_mark_grad_computed(h, 7) == -1
+        lib.smpc_gc_clear(h)
+        assert lib.smpc_gc_expected(h, 0, 1) == 0 and lib.smpc_gc_is_ready(h, 1) == 0
+    finally:
+        lib.smpc_gc_destroy(h)
+
+
+def test_bucket_planner(lib):
+    mb = 1 << 20
+    sizes = [mb // 2, mb // 2, mb // 2, 40 * mb, 70 * mb, 10 * mb, 30 * mb]
+    keys = [0] * len(sizes)
+    out = (ctypes.c_int * len(sizes))()
+    n = lib.smpc_plan_buckets(len(sizes), (ctypes.c_longlong * len(sizes))(*sizes), (ctypes.c_int * len(keys))(*keys),
+                              1 * mb, 100 * mb, out)
+    # first bucket closes at 1 MB, later ones at 100 MB
+    assert list(out) == [0, 0, 1, 1, 2, 2, 3] and n == 4
+    # tensors of different dtype never share a bucket
+    sizes, keys = [10, 10, 10, 10], [0, 1, 0, 1]
+    out = (ctypes.c_int * 4)()
+    n = lib.smpc_plan_buckets(4, (ctypes.c_longlong * 4)(*sizes), (ctypes.c_int * 4)(*keys), 1000, 1000, out)
+    assert n == 2 and out[0] == out[2] and out[1] == out[3] and out[0] != out[1]
+
+
+def test_timeline_writes_chrome_trace(lib):
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "timeline.json")
+        assert lib.smpc_timeline_create(path.encode(), 0) == 0
+        assert lib.smpc_timeline_enabled() == 1
+        lib.smpc_timeline_start_step()
+        lib.smpc_timeline_record_pipeline_event(0, b"fwd_mb0")
+        lib.smpc_timeline_record_pipeline_event(0, b"fwd_mb0")
+        lib.smpc_timeline_record_pipeline_event(1, b"bwd_mb1")
+        lib.smpc_timeline_end_step()
+        assert lib.smpc_timeline_num_events() >= 2
+        assert lib.smpc_timeline_flush() == 0
+        lib.smpc_timeline_destroy()
+        text = open(path).read()
+        assert "fwd_mb0" in text and "bwd_mb1" in text
+        data = json.loads(text)
+        names = [e["name"] for e in data["traceEvents"]]
+        assert names[0] == "step" and names[-1] == "step"
+
+
+def test_memory_metrics(lib):
+    lib.smpc_pool_record(1 << 20, 2 << 20, 1)
+    lib.smpc_pool_record(1 << 10, 0, 0)
+    out = (ctypes.c_longlong * 2)()
+    assert lib.smpc_get_and_reset_alloc_metrics(out) == 0
+    assert out[0] >= 1 and out[1] >= 1                  # successes, failures
+    assert lib.smpc_get_and_reset_alloc_metrics(out) == 0
+    assert out[0] == 0 and out[1] == 0
+
+
+def _bus_worker(rank, world):
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200.backend.collectives import CommGroup, RankType
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2})
+    comm = smp.state.comm
+    peer = 1 - rank
+    # point to point, including a payload larger than one socket buffer
+    big = bytes(range(256)) * 8192
+    comm.send({"from": rank, "blob": big}, peer, RankType.WORLD_RANK)
+    got = comm.recv_from(peer, RankType.WORLD_RANK)
+    assert got["from"] == peer and got["blob"] == big
+    # collectives on the control plane
+    assert comm.allgather(rank * 10, CommGroup.WORLD) == [0, 10]
+    if rank == 0:                                        # broadcast is sender-side; receivers call recv_from
+        comm.broadcast("hello", CommGroup.WORLD)
+    else:
+        assert comm.recv_from(0, RankType.WORLD_RANK) == "hello"
+    g = comm.gather(rank + 1, CommGroup.WORLD, 0)
+    if rank == 0:
+        assert g == [1, 2]
+    comm.barrier()
+    return True
+
+
+def test_message_bus_two_processes():
+    assert all(run_distributed(_bus_worker, 2))

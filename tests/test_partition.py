@@ -1,0 +1,89 @@
+"""Auto-partitioner pieces on mock inputs (reference test/torch/test_child_partition.py, test_partition.py):
+d'Hondt seat allocation, min-max contiguous segmentation, whole-model partitioning of toy modules and
+manual pins."""
+
+import torch
+import torch.nn as nn
+
+from smdistributed_modelparallel_b200.pipeline.partition import ModulePartitioner, dhondt_allocate, get_segments
+
+
+def test_dhondt_proportional():
+    assert dhondt_allocate([100, 50, 25], 7) == [4, 2, 1]
+    assert dhondt_allocate([1, 1, 1, 1], 4) == [1, 1, 1, 1]
+    assert sum(dhondt_allocate([3, 2, 1], 10)) == 10
+    # an unsplittable item never takes more than one seat
+    assert dhondt_allocate([100, 1], 3, splittable=[False, True]) == [1, 2]
+    assert dhondt_allocate([5.0], 0) == [0]
+
+
+def test_segments_minimise_the_maximum_load():
+    seg = get_segments([1, 1, 1, 1, 1, 1], 3)
+    assert seg == [0, 0, 1, 1, 2, 2]
+    seg = get_segments([5, 1, 1, 1, 1, 1], 2)
+    assert seg == [0, 1, 1, 1, 1, 1]
+    seg = get_segments([1, 2, 3, 4, 5, 6, 7, 8, 9], 3)
+    loads = [sum(c for c, s in zip(range(1, 10), seg) if s == j) for j in range(3)]
+    assert max(loads) == 17                                   # {1..5}=15 {6,7}=13 {8,9}=17
+    assert seg == sorted(seg)                                 # contiguous
+    # existing load on a device pushes work to the others
+    seg = get_segments([1, 1, 1, 1], 2, base_loads=[3, 0])
+    assert seg.count(1) > seg.count(0)
+    assert get_segments([], 3) == []
+
+
+class _Toy(nn.Module):
+    def __init__(self, widths):
+        super().__init__()
+        self.blocks = nn.Sequential(*[nn.Linear(w, w) for w in widths])
+        self.head = nn.Linear(widths[-1], 4)
+
+    def forward(self, x):
+        return self.head(self.blocks(x))
+
+
+def _loads(assign, model):
+    loads = {}
+    for m, dev in assign.items():
+        loads[dev] = loads.get(dev, 0) + sum(p.numel() for p in m.parameters(recurse=False))
+    return loads
+
+
+def test_partition_balances_parameters():
+    torch.manual_seed(0)
+    model = _Toy([64] * 8)
+    assign = ModulePartitioner(model, 2, memory_weight=1.0).partition()
+    assert assign[model] == 0                                 # the root lives on the first stage
+    for m in model.modules():
+        assert m in assign
+    loads = _loads(assign, model)
+    assert set(loads) == {0, 1}
+    assert max(loads.values()) / sum(loads.values()) < 0.7
+    devs = [assign[b] for b in model.blocks]
+    assert devs == sorted(devs)                               # sequential children stay contiguous
+
+
+def test_partition_four_way_and_manual_pin():
+    model = _Toy([32] * 12)
+    assign = ModulePartitioner(model, 4, memory_weight=1.0).partition()
+    assert set(assign[b] for b in model.blocks) == {0, 1, 2, 3}
+    pinned = model.blocks[0]
+    assign = ModulePartitioner(model, 2, memory_weight=1.0, manual=lambda m: 1 if m is pinned else None).partition()
+    assert assign[pinned] == 1
+
+
+def test_shared_parameters_are_colocated():
+    class Tied(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = nn.Embedding(50, 16)
+            self.mid = nn.Sequential(*[nn.Linear(16, 16) for _ in range(6)])
+            self.out = nn.Linear(16, 50, bias=False)
+            self.out.weight = self.emb.weight
+
+        def forward(self, x):
+            return self.out(self.mid(self.emb(x)))
+
+    model = Tied()
+    assign = ModulePartitioner(model, 2, memory_weight=1.0).partition()
+    assert assign[model.emb] == assign[model.out]
