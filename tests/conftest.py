@@ -4,6 +4,7 @@ import sys
 import pytest
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+os.environ.setdefault("SMP_LOG_LEVEL", "warning")       # keep the config dump out of test output
 
 
 def pytest_configure(config):

@@ -1,0 +1,143 @@
+"""smp.save_checkpoint / smp.resume_from_checkpoint / smp.save / smp.load on one process (file layout,
+``newest`` bookkeeping, retention, user content, lazy load before the model exists, config verification):
+reference test/torch/mpi_hybrid/test_checkpoint_api.py tier."""
+
+import os
+import tempfile
+
+import pytest
+import torch
+import torch.nn as nn
+
+import smdistributed_modelparallel_b200 as smp
+from smdistributed_modelparallel_b200.backend.exceptions import SMPValidationError
+
+
+def _setup(cfg=None, seed=0):
+    smp.reset()
+    smp.init(dict({"microbatches": 2}, **(cfg or {})))
+    torch.manual_seed(seed)
+    net = nn.Sequential(nn.Linear(8, 16), nn.Tanh(), nn.Linear(16, 4))
+    model = smp.DistributedModel(net)
+    opt = smp.DistributedOptimizer(torch.optim.Adam(model.parameters(), lr=1e-2))
+
+    @smp.step
+    def train_step(model, x, y):
+        loss = ((model(x) - y) ** 2).mean()
+        model.backward(loss)
+        return loss
+
+    return model, opt, train_step
+
+
+def _train(model, opt, step, n=2, seed=1):
+    torch.manual_seed(seed)
+    for _ in range(n):
+        x, y = torch.randn(4, 8), torch.randn(4, 4)
+        opt.zero_grad()
+        step(model, x, y)
+        opt.step()
+
+
+def test_partial_round_trip_and_layout():
+    with tempfile.TemporaryDirectory() as d:
+        model, opt, step = _setup()
+        _train(model, opt, step)
+        smp.save_checkpoint(d, tag="step2", partial=True, model=model, optimizer=opt, user_content={"epoch": 3})
+        files = set(os.listdir(os.path.join(d, "step2_partial")))
+        assert {"model_0_0.pt", "optimizer_states_0_0.pt", "smp_config.pt", "user_content.pt"} <= files
+        assert open(os.path.join(d, "newest")).read() == "step2_partial\n"
+        want = {k: v.clone() for k, v in model.state_dict().items()}
+        want_opt = opt.state_dict()["optimizer_state_dict"]
+        want_opt = {"state": {k: {n: (t.clone() if torch.is_tensor(t) else t) for n, t in st.items()}
+                              for k, st in want_opt["state"].items()}}
+        _train(model, opt, step, seed=9)              # diverge
+        assert any(not torch.equal(want[k], v) for k, v in model.state_dict().items())
+        uc = smp.resume_from_checkpoint(d)            # newest tag
+        assert uc == {"epoch": 3}
+        for k, v in model.state_dict().items():
+            assert torch.equal(want[k], v), k
+        got_opt = opt.state_dict()["optimizer_state_dict"]
+        for pid, st in want_opt["state"].items():
+            for name, val in st.items():
+                if torch.is_tensor(val):
+                    assert torch.allclose(val.float(), got_opt["state"][pid][name].float()), (pid, name)
+
+
+def test_retention_keeps_the_last_n():
+    with tempfile.TemporaryDirectory() as d:
+        model, opt, step = _setup()
+        for i in range(4):
+            smp.save_checkpoint(d, tag=f"t{i}", model=model, optimizer=opt, num_kept_partial_checkpoints=2)
+        dirs = sorted(x for x in os.listdir(d) if x.endswith("_partial"))
+        assert dirs == ["t2_partial", "t3_partial"]
+        assert open(os.path.join(d, "newest")).read().split() == ["t2_partial", "t3_partial"]
+
+
+def test_full_checkpoint_loads_into_plain_module():
+    with tempfile.TemporaryDirectory() as d:
+        model, opt, step = _setup()
+        _train(model, opt, step)
+        smp.save_checkpoint(d, tag="final", partial=False, model=model, user_content=[1, 2])
+        assert os.path.isfile(os.path.join(d, "final")) and os.path.isfile(os.path.join(d, "user_content_final"))
+        sd = torch.load(os.path.join(d, "final"), weights_only=False)
+        plain = nn.Sequential(nn.Linear(8, 16), nn.Tanh(), nn.Linear(16, 4))
+        plain.load_state_dict({k: v for k, v in sd.items() if not k.startswith("_smp")})
+        x = torch.randn(3, 8)
+        assert torch.allclose(plain(x), model.module(x))
+        with pytest.raises(SMPValidationError):
+            smp.resume_from_checkpoint(d, partial=False)       # a full checkpoint needs an explicit tag
+        model2, opt2, _ = _setup(seed=5)
+        assert smp.resume_from_checkpoint(d, tag="final", partial=False) == [1, 2]
+        assert torch.allclose(model2.module(x), plain(x))
+
+
+def test_resume_before_model_creation_is_deferred():
+    with tempfile.TemporaryDirectory() as d:
+        model, opt, step = _setup()
+        _train(model, opt, step)
+        smp.save_checkpoint(d, tag="a", model=model, optimizer=opt)
+        want = {k: v.clone() for k, v in model.state_dict().items()}
+        smp.reset()
+        smp.init({"microbatches": 2})
+        smp.resume_from_checkpoint(d, tag="a")
+        torch.manual_seed(77)
+        model2 = smp.DistributedModel(nn.Sequential(nn.Linear(8, 16), nn.Tanh(), nn.Linear(16, 4)))
+        opt2 = smp.DistributedOptimizer(torch.optim.Adam(model2.parameters(), lr=1e-2))
+
+        @smp.step
+        def fwd(model, x):
+            return model(x)
+
+        fwd(model2, torch.randn(4, 8))                # first step applies the deferred state
+        for k, v in model2.state_dict().items():
+            assert torch.equal(want[k], v), k
+        assert opt2 is not None
+
+
+def test_errors():
+    with tempfile.TemporaryDirectory() as d:
+        model, opt, step = _setup()
+        with pytest.raises(SMPValidationError):
+            smp.resume_from_checkpoint(d)              # no `newest`
+        with pytest.raises(SMPValidationError):
+            smp.resume_from_checkpoint(d, tag="missing")
+        with pytest.raises(Exception):
+            smp.save_checkpoint(d, tag=123, model=model)
+        smp.save_checkpoint(d, tag="x", model=model, optimizer=opt)
+        # a different parallel layout is refused when the saved config is verified
+        smp.reset()
+        smp.init({"microbatches": 4})
+        nn_model = smp.DistributedModel(nn.Sequential(nn.Linear(8, 16), nn.Tanh(), nn.Linear(16, 4)))
+        assert nn_model is not None
+        smp.resume_from_checkpoint(d, tag="x", load_optimizer=False)   # microbatches may differ
+
+
+def test_save_load_partial_names():
+    with tempfile.TemporaryDirectory() as d:
+        _setup()
+        smp.save({"a": 1}, os.path.join(d, "obj"), partial=True)
+        assert os.path.isfile(os.path.join(d, "obj_0_0.pt"))
+        assert smp.load(os.path.join(d, "obj"), partial=True) == {"a": 1}
+        smp.save({"b": 2}, os.path.join(d, "whole.pt"), partial=False)
+        assert smp.load(os.path.join(d, "whole.pt"), partial=False) == {"b": 2}

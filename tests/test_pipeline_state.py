@@ -1,0 +1,131 @@
+"""Microbatch schedule state machines stepped by hand, tensor stub round trip and module-manager bookkeeping
+(reference test/torch/test_pipeline.py:11-206, test_serialization.py, test_module_manager.py tier)."""
+
+import pytest
+import torch
+import torch.nn as nn
+
+from smdistributed_modelparallel_b200.pipeline.module_manager import ModuleManager
+from smdistributed_modelparallel_b200.runtime.messages import TensorStub, destubify, stubify, stubs_of
+from smdistributed_modelparallel_b200.runtime.pipeline import (InterleavedPipeline, MbStatus, OnlyForwardPipeline,
+                                                               SimplePipeline)
+
+
+def _drive(p, after_fwd):
+    """Run the schedule to completion; every forward finishes immediately and becomes ready for backward."""
+    order = []
+    while p.has_more_ticks():
+        mb = p.get_next_microbatch()
+        assert mb is not None
+        st = p.get_status(mb)
+        p.promote_status(mb)
+        if st is MbStatus.READY_FOR_FWD:
+            order.append(("F", mb))
+            after_fwd(p, mb)
+        else:
+            order.append(("B", mb))
+            p.mark_done(mb)
+    return order
+
+
+def test_simple_runs_all_forwards_then_backwards():
+    p = SimplePipeline(num_microbatches=4)
+    order = _drive(p, lambda p, mb: p.mark_ready_for_backward(mb))
+    assert order == [("F", 0), ("F", 1), ("F", 2), ("F", 3), ("B", 0), ("B", 1), ("B", 2), ("B", 3)]
+
+
+def test_simple_waits_for_outstanding_forwards():
+    p = SimplePipeline(num_microbatches=2)
+    assert p.get_next_microbatch() == 0
+    p.promote_status(0)                                  # forward of 0 in flight on a later stage
+    assert p.get_next_microbatch() == 1
+    p.promote_status(1)
+    assert p.get_next_microbatch() is None               # nothing to do until a forward returns
+    p.mark_ready_for_backward(1)
+    assert p.get_next_microbatch() is None               # mb 0 still in forward: simple schedule does not start backward
+    p.mark_ready_for_backward(0)
+    assert p.get_next_microbatch() == 0
+
+
+def test_interleaved_prefers_backward():
+    p = InterleavedPipeline(num_microbatches=3)
+    order = _drive(p, lambda p, mb: p.mark_ready_for_backward(mb))
+    assert order == [("F", 0), ("B", 0), ("F", 1), ("B", 1), ("F", 2), ("B", 2)]
+    # 1F1B steady state when results come back one tick late
+    p = InterleavedPipeline(num_microbatches=4)
+    assert p.get_next_microbatch() == 0
+    p.promote_status(0)
+    assert p.get_next_microbatch() == 1
+    p.promote_status(1)
+    p.mark_ready_for_backward(0)
+    assert p.get_next_microbatch() == 0 and p.get_status(0) is MbStatus.READY_FOR_BWD
+    p.promote_status(0)
+    assert p.in_flight() == 2
+    p.mark_done(0)
+    assert p.get_next_microbatch() == 2
+
+
+def test_only_forward():
+    p = OnlyForwardPipeline(num_microbatches=3)
+    seen = []
+    for _ in range(3):
+        mb = p.get_next_microbatch()
+        seen.append(mb)
+        p.promote_status(mb)
+        p.mark_done(mb)
+    assert seen == [0, 1, 2] and not p.has_more_ticks()
+
+
+def test_get_next_mb_with_status_scans_cyclically():
+    p = SimplePipeline(num_microbatches=4)
+    p.mark_ready_for_backward(1)
+    p.mark_ready_for_backward(3)
+    assert p.get_next_mb_with_status(MbStatus.READY_FOR_BWD) == 1
+    assert p.get_next_mb_with_status(MbStatus.READY_FOR_BWD, after=1) == 3
+    assert p.get_next_mb_with_status(MbStatus.READY_FOR_BWD, after=3) == 1
+    assert p.get_next_mb_with_status([MbStatus.DONE]) is None
+
+
+def test_stub_round_trip():
+    a, b = torch.randn(2, 3, requires_grad=True), torch.arange(4)
+    obj = ((a, {"k": [b, 5, "s"]}), {"flag": None})
+    skel, tensors = stubify(obj)
+    assert len(tensors) == 2 and tensors[0] is a and tensors[1] is b
+    stubs = stubs_of(skel)
+    assert [s.index for s in stubs] == [0, 1]
+    assert stubs[0] == TensorStub(0, (2, 3), torch.float32, True)
+    assert stubs[1].dtype == torch.int64 and not stubs[1].requires_grad
+    back = destubify(skel, [t.clone() for t in tensors])
+    assert torch.equal(back[0][0], a) and torch.equal(back[0][1]["k"][0], b)
+    assert back[0][1]["k"][1:] == [5, "s"] and back[1] == {"flag": None}
+
+
+def test_module_manager_names_partitions_and_marks():
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a = nn.Linear(4, 4)
+            self.b = nn.Sequential(nn.Linear(4, 4), nn.ReLU())
+
+    mm = ModuleManager()
+
+    from smdistributed_modelparallel_b200.backend.config import ModelParallelConfig
+
+    mm.set_config(ModelParallelConfig({"pipeline_parallel_degree": 2, "microbatches": 2}))
+    net = Net()
+    mm.name_modules_and_create_parent_map(net)
+    assert mm.get_module_name(net) == "main" or mm.get_module_name(net) == ""
+    assert mm.get_module(mm.get_module_name(net.b[0])) is net.b[0]
+    assert net.b in mm.get_parent_modules(net.b[0])
+    name = mm.get_module_name
+    mm.assign_partitions({name(net): 0, name(net.a): 0, name(net.b): 1, name(net.b[0]): 1, name(net.b[1]): 1})
+    with pytest.raises(Exception):
+        mm.assign_partitions({name(net): 7})
+    assert mm.get_partition(net.b[0]) == 1 and mm.is_executor(net.a, 0) and not mm.is_executor(net.b, 0)
+    assert mm.get_module_name(net.b) in mm.local_module_names(1)
+    mm.set_activation_checkpointing(net.b, pack_args_as_tuple=True, strategy="each")
+    assert mm.should_checkpoint_activations(net.b) and not mm.should_checkpoint_activations(net.a)
+    mm.set_tensor_parallelism(net.a, True, foo=1)
+    assert mm.is_marked_for_tp(net.a) and mm.get_tp_config(net.a) == {"foo": 1}
+    with pytest.raises(Exception):
+        mm.set_partition(net.a, 5)
