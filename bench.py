@@ -107,6 +107,84 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def library_baseline(args):
+    """N=1 stand-in for the reference's compute path: the stock HuggingFace GPT-J module (cuBLAS GEMMs through
+    F.linear, library attention / LayerNorm / softmax kernels), fp32 master weights with bf16 autocast and
+    torch's fused AdamW - none of this repo's kernels or engine.  Same model, batch geometry and timing."""
+    import torch
+    from transformers import GPTJConfig, GPTJForCausalLM
+
+    from smdistributed_modelparallel_b200.models.configs import MODEL_CONFIGS, param_count, train_flops_per_token
+
+    mcfg = dict(MODEL_CONFIGS[args.model])
+    if args.layers:
+        mcfg["num_layers"] = args.layers
+    seq = args.seq or mcfg["num_positions"]
+    micro, nmb = args.micro_batch or 4, args.microbatches or 2
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(1234)
+    cfg = GPTJConfig(vocab_size=mcfg["vocab_size"], n_positions=seq, n_embd=mcfg["hidden_size"],
+                     n_layer=mcfg["num_layers"], n_head=mcfg["num_attention_heads"], rotary_dim=mcfg["rotary_dim"],
+                     n_inner=mcfg["intermediate_size"], resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0,
+                     use_cache=False)
+    with torch.device(dev):
+        model = GPTJForCausalLM(cfg)
+    model.train()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, betas=(0.9, 0.95), weight_decay=0.1, fused=True)
+    vocab = mcfg["vocab_size"]
+    ids_dev = torch.randint(0, vocab, (micro * nmb, seq), device=dev)
+    host_ids = [torch.randint(0, vocab, (micro * nmb, seq)).pin_memory() for _ in range(4)]
+
+    def one_step(ids):
+        opt.zero_grad(set_to_none=True)
+        total = None
+        for mb in range(nmb):
+            chunk = ids[mb * micro:(mb + 1) * micro]
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = model(input_ids=chunk, labels=chunk).loss / nmb
+            loss.backward()
+            total = loss.detach() if total is None else total + loss.detach()
+        opt.step()
+        return total
+
+    for _ in range(max(args.warmup, 1)):
+        one_step(ids_dev)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        one_step(ids_dev)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_a = e0.elapsed_time(e1) / args.steps
+    e0.record()
+    last = None
+    for i in range(args.steps):
+        last = float(one_step(host_ids[i % 4].to(dev, non_blocking=True)).item())
+    e1.record()
+    torch.cuda.synchronize()
+    ms_b = e0.elapsed_time(e1) / args.steps
+    clocks = sampler.stop()
+    tokens = micro * nmb * seq
+    flops = train_flops_per_token(mcfg, seq)
+    print(json.dumps({
+        "metric": "training tokens/sec (device-timed, max over ranks), GPT-J-6B bf16 seq 2048",
+        "value": round(tokens / ms_a * 1e3, 1), "unit": "tokens/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(ms_a, 2), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16 autocast, fp32 master", "data": "synthetic tokens, random-init weights",
+        "impl": "baseline-library (HF GPTJForCausalLM + cuBLAS + torch fused AdamW)",
+        "config": {"model": args.model, "params": param_count(mcfg), "layers": mcfg["num_layers"],
+                   "global_batch": micro * nmb, "seq_len": seq, "microbatches": nmb, "micro_batch": micro,
+                   "parallelism": "dp1", "valid": not bool(args.layers)},
+        "model_tflops_per_gpu": round(tokens / ms_a * 1e3 * flops / 1e12, 1), "clocks": clocks,
+        "e2e": {"value": round(tokens / ms_b * 1e3, 1), "unit": "tokens/s", "h2d_bytes_per_step": micro * nmb * seq * 8,
+                "d2h_bytes_per_step": 4, "ms_per_step": round(ms_b, 2), "last_loss": last},
+        "gpu_launches": 0, "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 1)}), flush=True)
+    return 0
+
+
 def pick_parallelism(n, spec):
     """Returns (pp, tp, sdp, label)."""
     import re
@@ -123,6 +201,9 @@ def main():
     args = parse()
     if args.impl == "reference":
         return reference_arm(args)
+
+    if args.impl == "baseline" and int(os.environ.get("WORLD_SIZE", "1")) == 1 and args.model == "gpt-j-6b":
+        return library_baseline(args)
 
     import torch
     import torch.distributed as dist
@@ -225,6 +306,16 @@ def main():
     ms_b = e0.elapsed_time(e1) / args.steps
     wall_b = (time.perf_counter() - t0) * 1000 / args.steps
     clocks = sampler.stop() if smp.rank() == 0 else None
+
+    if os.environ.get("BENCH_TORCH_PROFILE"):
+        # diagnosis only (after the timed regions): one step under torch.profiler, chrome trace per rank
+        from torch.profiler import ProfilerActivity, profile
+        sync_all()
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            one_step(dev_ids)
+            sync_all()
+        os.makedirs(os.environ["BENCH_TORCH_PROFILE"], exist_ok=True)
+        prof.export_chrome_trace(os.path.join(os.environ["BENCH_TORCH_PROFILE"], f"trace_rank{smp.rank()}.json"))
 
     t = torch.tensor([ms_a, max(ms_b, wall_b)], device=dev, dtype=torch.float64)
     if n > 1:

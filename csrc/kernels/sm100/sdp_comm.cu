@@ -93,67 +93,97 @@ struct ReduceArgs {
   int adamw;
 };
 
+// One thread owns RU float4 vectors per trip (strided by the block so every load instruction is coalesced) and
+// pulls them from every rank in turn: RU x 16 B x 256 threads x CTAs stay in flight per source, which is what
+// it takes to cover NVLink latency (a single vector per thread leaves the links ~85 % idle).
+constexpr int RU = 4;
+
+__device__ __forceinline__ float4 ld_nc_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+
 __global__ void __launch_bounds__(256) sdp_reduce_kernel(ReduceArgs a) {
   if (threadIdx.x < a.nranks && threadIdx.x != a.rank) spin_ge(&a.ready[threadIdx.x], a.epoch);
   __syncthreads();
   const long long per = a.piece_elems * a.pieces_per_rank;
   const long long nvec = per >> 2;
   const long long pvec = a.piece_elems >> 2;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-    const long long q = i / pvec, e = i - q * pvec;
-    const long long goff = (q * a.nranks + a.rank) * pvec + e;
-    float4 v[MAX_RANKS];
+  const long long trip = (long long)blockDim.x * RU;
+  for (long long base = (long long)blockIdx.x * trip; base < nvec; base += (long long)gridDim.x * trip) {
+    long long idx[RU], goff[RU];
+    float4 acc[RU];
 #pragma unroll
-    for (int j = 0; j < MAX_RANKS; ++j)
-      if (j < a.nranks) v[j] = reinterpret_cast<const float4*>(a.peer_grad[j])[goff];
-    float4 s = v[0];
+    for (int u = 0; u < RU; ++u) {
+      idx[u] = base + (long long)u * blockDim.x + threadIdx.x;
+      const long long i = idx[u] < nvec ? idx[u] : 0;
+      const long long q = i / pvec;
+      goff[u] = (q * a.nranks + a.rank) * pvec + (i - q * pvec);
+      acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    // fixed rank order: the sum is bitwise identical on every run
 #pragma unroll
-    for (int j = 1; j < MAX_RANKS; ++j)
-      if (j < a.nranks) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
-    float g[4] = {s.x, s.y, s.z, s.w};
-    if (a.beta != 0.f) {
-      const float4 old = reinterpret_cast<const float4*>(a.grad_shard)[i];
-      g[0] += a.beta * old.x; g[1] += a.beta * old.y; g[2] += a.beta * old.z; g[3] += a.beta * old.w;
+    for (int j = 0; j < MAX_RANKS; ++j) {
+      if (j < a.nranks) {
+        float4 v[RU];
+        const float4* src = reinterpret_cast<const float4*>(a.peer_grad[j]);
+#pragma unroll
+        for (int u = 0; u < RU; ++u) v[u] = ld_nc_f4(src + goff[u]);
+#pragma unroll
+        for (int u = 0; u < RU; ++u) { acc[u].x += v[u].x; acc[u].y += v[u].y; acc[u].z += v[u].z; acc[u].w += v[u].w; }
+      }
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) g[k] *= a.scale;
-    if (a.mode == 0) {
-      reinterpret_cast<float4*>(a.grad_shard)[i] = make_float4(g[0], g[1], g[2], g[3]);
-      continue;
-    }
-    float4 p4 = reinterpret_cast<const float4*>(a.master)[i];
-    float4 m4 = reinterpret_cast<const float4*>(a.exp_avg)[i];
-    float4 s4 = reinterpret_cast<const float4*>(a.exp_avg_sq)[i];
-    float p[4] = {p4.x, p4.y, p4.z, p4.w}, m[4] = {m4.x, m4.y, m4.z, m4.w}, sq[4] = {s4.x, s4.y, s4.z, s4.w};
+    for (int u = 0; u < RU; ++u) {
+      const long long i = idx[u];
+      if (i >= nvec) continue;
+      float g[4] = {acc[u].x, acc[u].y, acc[u].z, acc[u].w};
+      if (a.beta != 0.f) {
+        const float4 old = reinterpret_cast<const float4*>(a.grad_shard)[i];
+        g[0] += a.beta * old.x; g[1] += a.beta * old.y; g[2] += a.beta * old.z; g[3] += a.beta * old.w;
+      }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      float gg = g[k] * a.grad_scale;
-      if (!a.adamw) gg += a.wd * p[k];
-      m[k] = a.beta1 * m[k] + (1.f - a.beta1) * gg;
-      sq[k] = a.beta2 * sq[k] + (1.f - a.beta2) * gg * gg;
-      float upd = (m[k] / a.bc1) / (sqrtf(sq[k] / a.bc2) + a.eps);
-      if (a.adamw) upd += a.wd * p[k];
-      p[k] -= a.lr * upd;
-    }
-    reinterpret_cast<float4*>(a.master)[i] = make_float4(p[0], p[1], p[2], p[3]);
-    reinterpret_cast<float4*>(a.exp_avg)[i] = make_float4(m[0], m[1], m[2], m[3]);
-    reinterpret_cast<float4*>(a.exp_avg_sq)[i] = make_float4(sq[0], sq[1], sq[2], sq[3]);
-    if (a.lowp != nullptr) {
-      if (a.lowp_dtype == SMPK_BF16) {
-        __nv_bfloat162 lo = __floats2bfloat162_rn(p[0], p[1]), hi = __floats2bfloat162_rn(p[2], p[3]);
-        uint2 w;
-        w.x = *reinterpret_cast<uint32_t*>(&lo);
-        w.y = *reinterpret_cast<uint32_t*>(&hi);
-        reinterpret_cast<uint2*>(a.lowp)[i] = w;
-      } else if (a.lowp_dtype == SMPK_F16) {
-        __half2 lo = __floats2half2_rn(p[0], p[1]), hi = __floats2half2_rn(p[2], p[3]);
-        uint2 w;
-        w.x = *reinterpret_cast<uint32_t*>(&lo);
-        w.y = *reinterpret_cast<uint32_t*>(&hi);
-        reinterpret_cast<uint2*>(a.lowp)[i] = w;
-      } else {
-        reinterpret_cast<float4*>(a.lowp)[i] = make_float4(p[0], p[1], p[2], p[3]);
+      for (int k = 0; k < 4; ++k) g[k] *= a.scale;
+      if (a.mode == 0) {
+        reinterpret_cast<float4*>(a.grad_shard)[i] = make_float4(g[0], g[1], g[2], g[3]);
+        continue;
+      }
+      float4 p4 = reinterpret_cast<const float4*>(a.master)[i];
+      float4 m4 = reinterpret_cast<const float4*>(a.exp_avg)[i];
+      float4 s4 = reinterpret_cast<const float4*>(a.exp_avg_sq)[i];
+      float p[4] = {p4.x, p4.y, p4.z, p4.w}, m[4] = {m4.x, m4.y, m4.z, m4.w}, sq[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float gg = g[k] * a.grad_scale;
+        if (!a.adamw) gg += a.wd * p[k];
+        m[k] = a.beta1 * m[k] + (1.f - a.beta1) * gg;
+        sq[k] = a.beta2 * sq[k] + (1.f - a.beta2) * gg * gg;
+        float upd = (m[k] / a.bc1) / (sqrtf(sq[k] / a.bc2) + a.eps);
+        if (a.adamw) upd += a.wd * p[k];
+        p[k] -= a.lr * upd;
+      }
+      reinterpret_cast<float4*>(a.master)[i] = make_float4(p[0], p[1], p[2], p[3]);
+      reinterpret_cast<float4*>(a.exp_avg)[i] = make_float4(m[0], m[1], m[2], m[3]);
+      reinterpret_cast<float4*>(a.exp_avg_sq)[i] = make_float4(sq[0], sq[1], sq[2], sq[3]);
+      if (a.lowp != nullptr) {
+        if (a.lowp_dtype == SMPK_BF16) {
+          __nv_bfloat162 lo = __floats2bfloat162_rn(p[0], p[1]), hi = __floats2bfloat162_rn(p[2], p[3]);
+          uint2 w;
+          w.x = *reinterpret_cast<uint32_t*>(&lo);
+          w.y = *reinterpret_cast<uint32_t*>(&hi);
+          reinterpret_cast<uint2*>(a.lowp)[i] = w;
+        } else if (a.lowp_dtype == SMPK_F16) {
+          __half2 lo = __floats2half2_rn(p[0], p[1]), hi = __floats2half2_rn(p[2], p[3]);
+          uint2 w;
+          w.x = *reinterpret_cast<uint32_t*>(&lo);
+          w.y = *reinterpret_cast<uint32_t*>(&hi);
+          reinterpret_cast<uint2*>(a.lowp)[i] = w;
+        } else {
+          reinterpret_cast<float4*>(a.lowp)[i] = make_float4(p[0], p[1], p[2], p[3]);
+        }
       }
     }
   }
@@ -181,7 +211,7 @@ SMPK_API int smpk_sdp_gather(void* stream, void* const* peer_shard, void* full, 
   for (int i = 0; i < MAX_RANKS; ++i) a.peer_shard[i] = i < nranks ? peer_shard[i] : nullptr;
   a.full = full; a.piece_bytes = piece_bytes; a.pieces_per_rank = pieces_per_rank;
   a.ready = reinterpret_cast<const uint32_t*>(ready); a.epoch = epoch; a.nranks = nranks; a.rank = rank;
-  if (ctas < 1) ctas = 48;
+  if (ctas < 1) ctas = 96;
   const long long need = (pieces_per_rank * nranks + 7) / 8;
   if (ctas > need) ctas = (int)(need < 1 ? 1 : need);
   sdp_gather_kernel<<<ctas, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
@@ -211,8 +241,8 @@ SMPK_API int smpk_sdp_reduce_adam(void* stream, void* const* peer_grad, float* g
   a.bc1 = bias_correction ? 1.f - powf(beta1, (float)step) : 1.f;
   a.bc2 = bias_correction ? 1.f - powf(beta2, (float)step) : 1.f;
   const long long nvec = piece_elems * pieces_per_rank / 4;
-  if (ctas < 1) ctas = 64;
-  long long g = (nvec + 255) / 256;
+  if (ctas < 1) ctas = 2 * smpk::num_sms();
+  long long g = (nvec + 256 * RU - 1) / (256 * RU);
   if (g < 1) g = 1;
   if (ctas > g) ctas = (int)g;
   sdp_reduce_kernel<<<ctas, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);

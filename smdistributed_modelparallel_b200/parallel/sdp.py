@@ -98,6 +98,36 @@ class Unit:
         return full.view(self.ppr, self.degree, self.piece)[:, r].reshape(-1)
 
 
+def _map_tensors(obj, fn):
+    if torch.is_tensor(obj):
+        return fn(obj)
+    if isinstance(obj, tuple):
+        return tuple(_map_tensors(o, fn) for o in obj)
+    if isinstance(obj, list):
+        return [_map_tensors(o, fn) for o in obj]
+    if isinstance(obj, dict):
+        return {k: _map_tensors(v, fn) for k, v in obj.items()}
+    return obj
+
+
+class _UnitBoundary(torch.autograd.Function):
+    """Identity on a unit's (differentiable) inputs.  Its backward runs after every other node of the unit -
+    all weight gradients of the unit are final - so that is where the unit's reduce-scatter is issued.  (Module
+    full-backward hooks cannot do this: they only see top-level tensor arguments, and the transformer layers take
+    one tuple.)"""
+
+    @staticmethod
+    def forward(ctx, engine, units, *tensors):
+        ctx.engine, ctx.units = engine, units
+        return tuple(t.view_as(t) for t in tensors)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        for u in ctx.units:
+            ctx.engine._reduce_unit(u)
+        return (None, None) + grads
+
+
 class ShardedDataParallelEngine:
     def __init__(self, model, params):
         from ..state_mod import state
@@ -186,7 +216,7 @@ class ShardedDataParallelEngine:
         for u in self.units:
             by_module.setdefault(u.module, []).append(u)
         for m, us in by_module.items():
-            self._hooks.append(m.register_forward_pre_hook(lambda mod, a, _us=us: self._pre_forward(_us)))
+            self._hooks.append(m.register_forward_pre_hook(lambda mod, a, _us=us: self._pre_forward(_us, a)))
             self._hooks.append(m.register_forward_hook(lambda mod, a, out, _us=us: self._post_forward(_us)))
             self._hooks.append(m.register_full_backward_pre_hook(lambda mod, g, _us=us: self._pre_backward(_us)))
             self._hooks.append(m.register_full_backward_hook(lambda mod, gi, go, _us=us: self._post_backward(_us, gi)))
@@ -276,7 +306,7 @@ class ShardedDataParallelEngine:
             if nxt.full is None and nxt.numel <= self.max_live:
                 self._issue_gather(nxt)
 
-    def _pre_forward(self, units):
+    def _pre_forward(self, units, args=None):
         for u in units:
             if not self._order_frozen and u not in self._order:
                 self._order.append(u)
@@ -284,7 +314,16 @@ class ShardedDataParallelEngine:
                 u.recompute_seen = True
             self._ensure(u, lazy_ok=True)
             u.users += 1
-        self._prefetch_after(units[-1], +1)
+        if not self._in_backward:            # a recomputed forward must not prefetch units that are already done
+            self._prefetch_after(units[-1], +1)
+        if args is None or not torch.is_grad_enabled():
+            return None
+        found = []
+        _map_tensors(args, lambda t: found.append(t) if t.requires_grad else None)
+        if not found:
+            return None                      # nothing to hang the boundary on: flushed at the end of backward
+        outs = iter(_UnitBoundary.apply(self, units, *found))
+        return _map_tensors(args, lambda t: next(outs) if t.requires_grad else t)
 
     def _post_forward(self, units):
         for u in units:
@@ -402,6 +441,13 @@ class ShardedDataParallelEngine:
             self._finish_one_reduce()
         if self.fabric is not None:
             self.fabric.wait_reduces()
+        for u in self.units:                 # a prefetch nobody consumed would be stale after the optimizer step
+            if u.full is None and u.gather_work is not None:
+                if not self.fused:
+                    u.gather_work.wait()
+                else:
+                    torch.cuda.current_stream(self.device).wait_event(u.gather_work)
+                u.gather_work, u._pending_full = None, None
         if not sync:
             return
         scale = 1.0 / self.world

@@ -22,6 +22,8 @@ backend/ds_config_defaults.json:6-27)
 from __future__ import annotations
 
 import ctypes
+import os
+import sys
 
 import torch
 import torch.distributed as dist
@@ -29,7 +31,15 @@ import torch.distributed as dist
 from ..ops import _native as N
 from .fused_tp import MAX_RANKS, SymmetricBuffer, _CommDesc, _ptr_array
 
-NSLOT = 2
+NSLOT = 3                     # gradient slots allocated up front
+MAX_SLOTS = 8
+_DEBUG = os.environ.get("SMP_SDP_DEBUG", "0") == "1"
+
+
+def _dbg(fab, *what):
+    if _DEBUG:
+        print(f"[sdp r{fab.rank}]", *what, file=sys.stderr, flush=True)
+
 COPY_ROWS = 8
 DEFAULT_ROW = 4096            # row width (elements) of units without a designated first weight
 
@@ -61,14 +71,18 @@ class PeerFabric:
         self.shards = SymmetricBuffer(max(total, 256), None, self.rank, None, pg=self.pg)
         self.max_numel = max((u.numel for u in units), default=8)
         self.slot_bytes = (self.max_numel * 4 + 255) // 256 * 256
-        self.grads = SymmetricBuffer(NSLOT * self.slot_bytes, None, self.rank, None, pg=self.pg)
+        # gradient slots: one symmetric allocation each; the pool grows (collectively, same order on every rank)
+        # when more units are in backward at once than there are slots - e.g. a tied embedding whose gradient
+        # stays open from the LM head to the very end of backward
+        self.slots = []
         # flag words: params_ready[8] | slot s: grad_ready[8] consumed[8]
-        self.flags = SymmetricBuffer((1 + 2 * NSLOT) * MAX_RANKS * 4, None, self.rank, None, pg=self.pg)
+        self.flags = SymmetricBuffer((1 + 2 * MAX_SLOTS) * MAX_RANKS * 4, None, self.rank, None, pg=self.pg)
         max_rows = max((u.numel // u.row for u in units), default=64)
         self.blk_flags = torch.zeros(max_rows // 64 + 8, dtype=torch.int32, device=self.dev)
-        self.counter = torch.zeros(NSLOT, dtype=torch.int32, device=self.dev)
+        self.counter = torch.zeros(MAX_SLOTS, dtype=torch.int32, device=self.dev)
         self.param_epoch = 0
-        self.slot_uses = 0
+        for _ in range(NSLOT):
+            self._add_slot()
         self.side = torch.cuda.Stream(device=self.dev)
         self.reduce_stream = torch.cuda.Stream(device=self.dev)
         self.reduce_events = []
@@ -88,6 +102,7 @@ class PeerFabric:
         """Everything queued on the current stream so far (optimizer writes of the 16-bit shard) becomes
         visible to the peers as parameter epoch ``param_epoch + 1``."""
         self.param_epoch += 1
+        _dbg(self, "publish params epoch", self.param_epoch)
         peers = _ptr_array([self._flag_ptr(j, 0) for j in range(self.n)])
         N.call("smpk_flags_signal", N.stream_ptr(self.dev), ctypes.cast(peers, ctypes.c_void_p), self.n, self.rank,
                self.param_epoch)
@@ -100,10 +115,11 @@ class PeerFabric:
     def gather(self, u, full, stream=None):
         """Stand-alone striped all-gather of ``u`` into ``full`` (current or given stream)."""
         es = full.element_size()
+        _dbg(self, "gather", u.name, "epoch", self.param_epoch)
         ps = _ptr_array(self._peer_shards(u))
         N.call("smpk_sdp_gather", N.stream_ptr(self.dev) if stream is None else stream.cuda_stream,
                ctypes.cast(ps, ctypes.c_void_p), full.data_ptr(), u.piece * es, u.ppr, self.flags.ptr, self.param_epoch,
-               self.n, self.rank, 48)
+               self.n, self.rank, 0)
         N.count_launch()
 
     def defer_to_gemm(self, u, full):
@@ -113,6 +129,7 @@ class PeerFabric:
         def run(gemm_args):
             pending_gathers.pop(key, None)
             u.lazy_pending = False
+            _dbg(self, "gemm-gather", u.name, gemm_args, "epoch", self.param_epoch)
             if gemm_args is None:                     # consumer cannot run the fused kernel: gather now
                 self.gather(u, full)
                 return None
@@ -136,16 +153,33 @@ class PeerFabric:
                 run(None)
 
     # ------------------------------------------------------------------ gradient slots
+    def _add_slot(self):
+        if len(self.slots) >= MAX_SLOTS:
+            raise RuntimeError("sharded data parallelism: more than 8 units have gradients in flight at once")
+        buf = SymmetricBuffer(self.slot_bytes, None, self.rank, None, pg=self.pg)
+        self.slots.append({"buf": buf, "uses": 0, "busy": False, "event": None})
+        return len(self.slots) - 1
+
     def acquire_slot(self, u):
         """fp32 [numel] gradient buffer for ``u`` in peer-visible memory (zeroed), once every peer has read the
-        slot's previous contents."""
-        s, e = self.slot_uses % NSLOT, self.slot_uses // NSLOT + 1
-        self.slot_uses += 1
+        slot's previous contents.  Every rank runs the same program, so slot choices agree without talking."""
+        s = next((i for i, sl in enumerate(self.slots) if not sl["busy"]), None)
+        if s is None:
+            s = self._add_slot()
+        sl = self.slots[s]
+        sl["uses"] += 1
+        sl["busy"] = True
+        e = sl["uses"]
+        _dbg(self, "acquire", u.name, "slot", s, "use", e)
         stream = N.stream_ptr(self.dev)
         if e > 1:
-            N.call("smpk_flags_wait", stream, self.flags.ptr + 4 * MAX_RANKS * (2 + 2 * s), self.n, -1, e - 1)
+            # peers: epoch flags in peer memory; this rank's own reduce kernel (side stream): a CUDA event, so
+            # no kernel on this GPU ever spins on another kernel of this GPU
+            N.call("smpk_flags_wait", stream, self.flags.ptr + 4 * MAX_RANKS * (2 + 2 * s), self.n, self.rank, e - 1)
             N.count_launch()
-        buf = self.grads.view(torch.float32, u.numel, s * self.slot_bytes)
+            if sl["event"] is not None:
+                torch.cuda.current_stream(self.dev).wait_event(sl["event"])
+        buf = sl["buf"].view(torch.float32, u.numel)
         buf.zero_()
         u.slot = (s, e)
         return buf
@@ -154,11 +188,12 @@ class PeerFabric:
         """Signal this rank's gradient slot complete, then (side stream) sum every rank's slot over this rank's
         stripes into ``u.grad_shard`` - or straight through Adam when ``adam`` carries the hyper-parameters."""
         s, e = u.slot
+        _dbg(self, "reduce", u.name, "slot", s, "use", e, "adam" if adam else "")
         cur = torch.cuda.current_stream(self.dev)
         peers = _ptr_array([self._flag_ptr(j, 1 + 2 * s) for j in range(self.n)])
         N.call("smpk_flags_signal", cur.cuda_stream, ctypes.cast(peers, ctypes.c_void_p), self.n, self.rank, e)
         self.reduce_stream.wait_stream(cur)
-        pg = _ptr_array([self.grads.peer_ptrs[j] + s * self.slot_bytes for j in range(self.n)])
+        pg = _ptr_array([self.slots[s]["buf"].peer_ptrs[j] for j in range(self.n)])
         pc = _ptr_array([self._flag_ptr(j, 2 + 2 * s) for j in range(self.n)])
         ready = self.flags.ptr + 4 * MAX_RANKS * (1 + 2 * s)
         rs = self.reduce_stream.cuda_stream
@@ -167,18 +202,20 @@ class PeerFabric:
                 self.rank)
         if adam is None:
             N.call("smpk_sdp_reduce_adam", *common, None, None, None, None, 0, *tail, 1.0, 1.0, 0,
-                   0.0, 0.0, 0.0, 0.0, 0.0, 1, 0, 0, 1.0, 64)
+                   0.0, 0.0, 0.0, 0.0, 0.0, 1, 0, 0, 1.0, 0)
         else:
             st = adam["state"]
             N.call("smpk_sdp_reduce_adam", *common, u.master.data.data_ptr(), st["exp_avg"].data_ptr(),
                    st["exp_avg_sq"].data_ptr(), u.shard.data_ptr(), N.dtype_code(u.shard.dtype), *tail,
                    float(adam["scale"]), 1.0, 1, float(adam["lr"]), float(adam["beta1"]), float(adam["beta2"]),
                    float(adam["eps"]), float(adam["wd"]), int(adam["step"]), int(adam["adamw"]),
-                   int(adam["bias_correction"]), 1.0, 64)
+                   int(adam["bias_correction"]), 1.0, 0)
         N.count_launch(2)
         ev = torch.cuda.Event()
         ev.record(self.reduce_stream)
         self.reduce_events.append(ev)
+        self.slots[s]["event"] = ev
+        self.slots[s]["busy"] = False
 
     def wait_reduces(self):
         cur = torch.cuda.current_stream(self.dev)

@@ -52,6 +52,10 @@ def _entry(rank, world, port, fn, args, queue, use_cuda=False):
     if not use_cuda:
         os.environ["CUDA_VISIBLE_DEVICES"] = ""
     sys.path.insert(0, ROOT)
+    dump_after = float(os.environ.get("SMP_TEST_HANG_DUMP_S", "0"))
+    if dump_after > 0:                       # where is every thread if the worker is still running by then?
+        import faulthandler
+        faulthandler.dump_traceback_later(dump_after, exit=True)
     try:
         out = _to_wire(fn(rank, world, *args))
         queue.put((rank, "ok", out))
@@ -61,6 +65,7 @@ def _entry(rank, world, port, fn, args, queue, use_cuda=False):
 
 
 def run_distributed(fn, world, *args, timeout=240, use_cuda=False):
+    timeout = float(os.environ.get("SMP_TEST_TIMEOUT_S", timeout))
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()

@@ -63,6 +63,12 @@ def _worker(rank, world, bf16, ckpt_dir, act_ckpt):
     uc = smp.resume_from_checkpoint(ckpt_dir, tag="t1", partial=True)
     after = model.state_dict()
     rt = max((after[k].float() - before[k].float()).abs().max().item() for k in before)
+    if rt > 1e-6 and rank == 0:
+        import sys
+        for k in before:
+            d = (after[k].float() - before[k].float()).abs().max().item()
+            if d > 1e-6:
+                print("DIFF", k, d, file=sys.stderr)
     files = sorted(os.listdir(os.path.join(ckpt_dir, "t1_partial")))
     return {"worst": worst, "units": n_units, "roundtrip": rt, "files": files, "uc": uc}
 

@@ -81,7 +81,7 @@ def main():
 
     def gather():
         N.call("smpk_sdp_gather", stream, ctypes.cast(ps, ctypes.c_void_p), full.data_ptr(), piece * 2, ppr, flags.ptr, 1,
-               n, rank, 48)
+               n, rank, 0)
 
     gather()
     torch.cuda.synchronize()
@@ -156,7 +156,7 @@ def main():
         N.call("smpk_flags_signal", stream, ctypes.cast(pready, ctypes.c_void_p), n, rank, ep[0])
         N.call("smpk_sdp_reduce_adam", stream, ctypes.cast(pgp, ctypes.c_void_p), grad_shard.data_ptr(), None, None, None,
                None, 0, piece, ppr, flags.ptr + 4 * MAX_RANKS, ctypes.cast(pcons, ctypes.c_void_p), counter.data_ptr(),
-               ep[0], n, rank, 1.0, beta, 0, 0.0, 0.0, 0.0, 0.0, 0.0, 1, 0, 0, 1.0, 64)
+               ep[0], n, rank, 1.0, beta, 0, 0.0, 0.0, 0.0, 0.0, 0.0, 1, 0, 0, 1.0, 0)
         # the slot may only be rewritten once every peer has read it
         N.call("smpk_flags_wait", stream, flags.ptr + 4 * MAX_RANKS * 2, n, -1, ep[0])
 
@@ -177,7 +177,7 @@ def main():
         N.call("smpk_sdp_reduce_adam", stream, ctypes.cast(pgp, ctypes.c_void_p), grad_shard.data_ptr(), master.data_ptr(),
                m1.data_ptr(), v1.data_ptr(), lowp.data_ptr(), N.dtype_code(lowp.dtype), piece, ppr, flags.ptr + 4 * MAX_RANKS,
                ctypes.cast(pcons, ctypes.c_void_p), counter.data_ptr(), ep[0], n, rank, 1.0 / n, 0.0, 1, 1e-3, 0.9, 0.95,
-               1e-8, 0.1, step[0], 1, 1, 1.0, 64)
+               1e-8, 0.1, step[0], 1, 1, 1.0, 0)
         N.call("smpk_flags_wait", stream, flags.ptr + 4 * MAX_RANKS * 2, n, -1, ep[0])
 
     reduce_adam()
