@@ -31,6 +31,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 
+METRIC_NAMES = {"gpt-j-6b": "GPT-J-6B", "gpt-neox-20b": "GPT-NeoX-20B", "gpt2-xl": "GPT-2-XL-1.5B",
+                "bert-large": "BERT-large", "roberta-large": "RoBERTa-large"}
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -43,6 +47,8 @@ def parse():
     ap.add_argument("--microbatches", type=int, default=0)
     ap.add_argument("--parallelism", default="", help="e.g. tp2, pp2, pp2tp4, sdp8, dp2 (default: chosen per N)")
     ap.add_argument("--checkpoint", type=int, default=-1, help="activation checkpointing (1/0, default auto)")
+    ap.add_argument("--active-microbatches", type=int, default=0, help="pipeline window (default: config default)")
+    ap.add_argument("--offload", type=int, default=0, help="offload checkpointed activations to pinned host memory")
     ap.add_argument("--layers", type=int, default=0, help="debug only: override layer count (marks the run invalid)")
     return ap.parse_args()
 
@@ -230,6 +236,10 @@ def main():
             "ddp": n > 1, "delayed_parameter_initialization": True, "pipeline": "interleaved"}
     if sdp > 1:
         conf["sharded_data_parallel_degree"] = sdp
+    if args.active_microbatches and pp > 1:
+        conf["active_microbatches"] = args.active_microbatches
+    if args.offload:
+        conf["offload_activations"] = True
     if tp > 1:
         conf["prescaled_batch"] = False
     os.environ.setdefault("SMP_LOG_LEVEL", "warning")
@@ -241,7 +251,7 @@ def main():
 
     with smp.model_creation(tensor_parallelism=tp > 1, dtype=torch.bfloat16):
         module = smp.nn.DistributedTransformerLMHead(**mcfg)
-    use_ckpt = args.checkpoint if args.checkpoint >= 0 else 0
+    use_ckpt = args.checkpoint if args.checkpoint >= 0 else (1 if args.model == "gpt-neox-20b" else 0)
     if use_ckpt:
         smp.set_activation_checkpointing(module.transformer.seq_layers, pack_args_as_tuple=True, strategy="each")
     model = smp.DistributedModel(module)
@@ -326,14 +336,16 @@ def main():
         e2e = tokens_per_step / (ms_b / 1000)
         flops = train_flops_per_token(mcfg, seq) * (4.0 / 3.0 if use_ckpt else 1.0)
         line = {
-            "metric": "training tokens/sec (device-timed, max over ranks), GPT-J-6B bf16 seq 2048",
+            "metric": f"training tokens/sec (device-timed, max over ranks), {METRIC_NAMES.get(args.model, args.model)} bf16 seq {seq}",
             "value": round(value, 1), "unit": "tokens/s", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms_a, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic tokens, random-init weights",
             "impl": "baseline-nccl-cublas" if baseline else "b200",
             "config": {"model": args.model, "params": param_count(mcfg), "layers": mcfg["num_layers"],
                        "global_batch": global_batch, "seq_len": seq, "microbatches": nmb, "micro_batch": micro,
-                       "parallelism": label, "tp_comm": tp_ops.get_comm_mode() if tp > 1 else None, "activation_checkpointing": bool(use_ckpt), "optimizer": "AdamW fp32 master",
+                       "parallelism": label, "tp_comm": tp_ops.get_comm_mode() if tp > 1 else None, "activation_checkpointing": bool(use_ckpt), "offload_activations": bool(args.offload),
+                       "active_microbatches": conf.get("active_microbatches", nmb) if pp > 1 else None,
+                       "optimizer": "AdamW fp32 master",
                        "l2": "working set (12 GB of bf16 weights per step) >> 126 MB L2; no explicit flush needed",
                        "valid": not bool(args.layers)},
             "model_tflops_per_gpu": round(value * flops / n / 1e12, 1),

@@ -29,6 +29,7 @@ What is different (by design):
 
 from __future__ import annotations
 
+import threading
 import traceback
 from dataclasses import dataclass, field
 
@@ -89,8 +90,11 @@ class PipelineP2P:
         self.state.module_manager.record_hop(nbytes)
         self._reap()
 
-    def recv(self, metas, src, device):
-        """metas: [(shape, dtype)] -> list of tensors (waits for arrival on the current stream)."""
+    def recv(self, metas, src, device, defer=False):
+        """metas: [(shape, dtype)] -> list of tensors.  The receives are posted now (posting order must follow
+        message order); the current stream waits for them now, or - with ``defer`` - when the caller later runs
+        the returned ``finish()`` (results stashed for a task that resumes later must not stall whatever the
+        compute stream is doing meanwhile)."""
         group = self.state.pp_p2p_groups[(src, self.me)]
         out, works = [], []
         for shape, dtype in metas:
@@ -98,9 +102,13 @@ class PipelineP2P:
             buf = torch.empty(shape, dtype=wire_dtype, device=device)
             works.append(dist.irecv(buf, src=src, group=group))
             out.append(buf)
-        for w in works:
-            w.wait()
-        return [b.to(torch.bool) if dt == torch.bool else b for b, (_, dt) in zip(out, metas)]
+
+        def finish():
+            for w in works:
+                w.wait()
+            return [b.to(torch.bool) if dt == torch.bool else b for b, (_, dt) in zip(out, metas)]
+
+        return finish if defer else finish()
 
     def _reap(self):
         self._inflight = [(w, t) for (w, t) in self._inflight if not w.is_completed()]
@@ -109,6 +117,87 @@ class PipelineP2P:
         for w, _ in self._inflight:
             w.wait()
         self._inflight = []
+
+
+_task_local = threading.local()
+
+
+class _Task:
+    """A microbatch running in its own thread.  Exactly one thread holds the baton at any time: the scheduler
+    (main thread) or one task, so the engine stays logically single-threaded; threads only give every
+    microbatch its own suspendable Python stack."""
+
+    def __init__(self, sched, mb, phase):
+        self.sched, self.mb, self.phase = sched, mb, phase
+        self.waiting_key = None
+        self.finished = False
+        self.error = None
+        self.resume_evt = threading.Event()
+        self.thread = threading.Thread(target=self._main, name=f"smp-mb{mb}", daemon=True)
+
+    def _main(self):
+        srv = self.sched.server
+        self.resume_evt.wait()
+        self.resume_evt.clear()
+        try:
+            if srv.state.device.type == "cuda":
+                torch.cuda.set_device(srv.state.device)          # device and stream selection are per thread
+            _task_local.task = self
+            srv._run_microbatch(self.mb, self.phase)
+        except BaseException as e:                               # noqa: BLE001 - re-raised on the main thread
+            self.error = e
+        finally:
+            _task_local.task = None
+            self.finished = True
+            self.sched.baton.set()
+
+    def suspend(self, key):
+        self.waiting_key = key
+        self.sched.baton.set()                                   # hand the baton back ...
+        self.resume_evt.wait()                                   # ... until the scheduler picks this task again
+        self.resume_evt.clear()
+        self.waiting_key = None
+
+
+class _Scheduler:
+    """Deterministic microbatch scheduling on the pipeline leader.
+
+    Rule: while fewer than ``window`` microbatches are in flight and some have not started, start the next
+    one; otherwise resume the task that has been suspended longest, blocking until the result it waits for has
+    arrived.  Nothing depends on message timing, so every tensor-parallel rank of a stage issues the same
+    sequence of kernels and collectives (the reference gets this from its deterministic server queue, reference
+    test/torch/mpi_4ps/test_deterministic.py:17-122), and the host runs ahead of the GPUs: the order in which
+    work is *enqueued* is a 1F1B-style interleave, and the streams + NCCL p2p dependencies pipeline it."""
+
+    def __init__(self, server, jobs, window):
+        self.server, self.jobs, self.window = server, list(jobs), window
+        self.baton = threading.Event()
+
+    def _switch_to(self, task):
+        self.baton.clear()
+        task.resume_evt.set()
+        self.baton.wait()
+        if task.error is not None:
+            raise task.error
+
+    def run(self):
+        srv = self.server
+        waiting = []                      # suspended tasks, oldest first
+        nxt = 0
+        while nxt < len(self.jobs) or waiting:
+            if nxt < len(self.jobs) and len(waiting) < self.window:
+                task = _Task(self, *self.jobs[nxt])
+                nxt += 1
+                task.thread.start()
+            else:
+                task = waiting.pop(0)
+                while task.waiting_key not in srv.stash:
+                    srv._pump_one(50)
+            self._switch_to(task)
+            if not task.finished:
+                waiting.append(task)
+            else:
+                task.thread.join()
 
 
 class ExecutionServer:
@@ -257,12 +346,13 @@ class ExecutionServer:
             self._serve_forward(src, msg, tensors)
         elif isinstance(msg, ForwardResult):
             metas = [(s.shape, s.dtype) for s in stubs_of(msg.skeleton)] if msg.error is None else []
-            self.stash[("F", msg.call_id)] = (msg, self.p2p.recv(metas, src, dev))
+            self.stash[("F", msg.call_id)] = (msg, self.p2p.recv(metas, src, dev, defer=True))
         elif isinstance(msg, BackwardRequest):
             grads = self.p2p.recv([(shape, dt) for _, shape, dt in msg.grad_meta], src, dev)
             self._serve_backward(src, msg, grads)
         elif isinstance(msg, BackwardResult):
-            grads = self.p2p.recv([(shape, dt) for _, shape, dt in msg.grad_meta], src, dev) if msg.error is None else []
+            grads = self.p2p.recv([(shape, dt) for _, shape, dt in msg.grad_meta], src, dev, defer=True) \
+                if msg.error is None else (lambda: [])
             self.stash[("B", msg.call_id)] = (msg, grads)
         elif isinstance(msg, StepDone):
             self._done_msg = msg
@@ -278,15 +368,19 @@ class ExecutionServer:
             raise SMPRuntimeError(f"unexpected pipeline message {type(msg).__name__}")
 
     def _wait_for(self, key):
-        """Block until stash[key] exists, serving requests (and, on the leader, starting further
-        microbatches) meanwhile."""
-        while key not in self.stash:
-            if self._pump_one(0):
-                continue
-            if self.is_leader and self._step_ctx is not None and self._start_nested_task():
-                continue
-            self._pump_one(20)
-        return self.stash.pop(key)
+        """Block until the result ``key`` has arrived and return (message, tensors).
+
+        Inside a leader task (see ``_Scheduler``) the task is suspended and the scheduler decides what runs
+        next; elsewhere (a non-leader stage waiting for a nested call) requests are served meanwhile."""
+        task = getattr(_task_local, "task", None)
+        if task is not None:
+            task.suspend(key)
+        else:
+            while key not in self.stash:
+                if not self._pump_one(0):
+                    self._pump_one(20)
+        msg, finish = self.stash.pop(key)
+        return msg, finish()
 
     # ================================================================== forward across ranks
     def _remote_forward(self, module_name, span, owner, args, kwargs):
@@ -406,58 +500,37 @@ class ExecutionServer:
         self.deferred_bwd[mb] = (tuple(tensors), tuple(grads))
 
     # ================================================================== the step
-    def _start_nested_task(self) -> bool:
-        ctx = self._step_ctx
-        if ctx is None or ctx["depth"] >= ctx["max_depth"]:
-            return False
-        return self._run_next_task(nested=True)
-
-    def _run_next_task(self, nested=False) -> bool:
+    def _run_microbatch(self, mb, phase):
+        """One microbatch on the leader: the step function (forward; ``model.backward`` only registers the
+        backward) and / or the registered backward, per ``phase`` in {"both", "fwd", "bwd"}."""
         ctx = self._step_ctx
         pipe = self.state.pipeline
-        mb = pipe.get_next_microbatch()
-        if mb is None:
-            return False
-        status = pipe.get_status(mb)
-        if status is MbStatus.READY_FOR_FWD and pipe.in_flight() >= ctx["active"]:
-            # budget exhausted: only a backward may start now
-            mb = pipe.get_next_mb_with_status(MbStatus.READY_FOR_BWD)
-            if mb is None:
-                return False
-            status = MbStatus.READY_FOR_BWD
-        if nested and status is MbStatus.READY_FOR_BWD and not ctx["nested_backward"]:
-            return False
-        pipe.promote_status(mb)
-        ctx["depth"] += 1
-        try:
-            st = self.state
-            prev = st.microbatch
+        st = self.state
+        st.microbatch = mb
+        if phase in ("both", "fwd"):
+            pipe.promote_status(mb)
+            self.core.timeline_record_pipeline_event(mb, "fwd_start")
+            fn, a, k = ctx["func"], ctx["args"][mb], ctx["kwargs"][mb]
+            out = fn(*a, **k)
             st.microbatch = mb
-            if status is MbStatus.READY_FOR_FWD:
-                self.core.timeline_record_pipeline_event(mb, "fwd_start")
-                fn, a, k = ctx["func"], ctx["args"][mb], ctx["kwargs"][mb]
-                out = fn(*a, **k)
-                ctx["outputs"][mb] = map_structure(lambda x: x.detach() if torch.is_tensor(x) else x, out) \
-                    if ctx["detach"] else out
-                if mb in self.deferred_bwd:
-                    pipe.mark_ready_for_backward(mb)
-                else:
-                    pipe.mark_done(mb)
+            ctx["outputs"][mb] = map_structure(lambda x: x.detach() if torch.is_tensor(x) else x, out) \
+                if ctx["detach"] else out
+            if mb in self.deferred_bwd:
+                pipe.mark_ready_for_backward(mb)
             else:
-                self.core.timeline_record_pipeline_event(mb, "bwd_start")
-                tensors, grads = self.deferred_bwd.pop(mb)
-                self._backward_segment(mb, tensors, grads)
-                self.boundaries.pop(mb, None)
-                del tensors, grads
-                for r in self.core.get_pp_group():
-                    if r != self.me:
-                        self.comm.server_send(("mb_done", mb), r)
                 pipe.mark_done(mb)
-                self.core.timeline_record_pipeline_event(mb, "bwd_end")
-            st.microbatch = prev
-        finally:
-            ctx["depth"] -= 1
-        return True
+        if phase in ("both", "bwd") and mb in self.deferred_bwd:
+            pipe.promote_status(mb)
+            self.core.timeline_record_pipeline_event(mb, "bwd_start")
+            tensors, grads = self.deferred_bwd.pop(mb)
+            self._backward_segment(mb, tensors, grads)
+            self.boundaries.pop(mb, None)
+            del tensors, grads
+            for r in self.core.get_pp_group():
+                if r != self.me:
+                    self.comm.server_send(("mb_done", mb), r)
+            pipe.mark_done(mb)
+            self.core.timeline_record_pipeline_event(mb, "bwd_end")
 
     def run_step(self, step_fn, args, kwargs, num_mb):
         st = self.state
@@ -470,12 +543,14 @@ class ExecutionServer:
         if self.is_leader:
             a, k = step_fn.splitter.preprocess_args_all_mbs(args, kwargs, num_mb)
             self._step_ctx = {"func": step_fn.func, "args": a, "kwargs": k, "outputs": [None] * num_mb,
-                              "detach": step_fn.detach_outputs, "depth": 0, "max_depth": max(1, st.cfg.active_microbatches),
-                              "active": st.cfg.active_microbatches, "nested_backward": st.cfg.pipeline == "interleaved"}
+                              "detach": step_fn.detach_outputs}
             try:
-                while pipe.has_more_ticks():
-                    if not self._run_next_task():
-                        self._pump_one(20)
+                window = max(1, int(st.cfg.active_microbatches))
+                if st.cfg.pipeline == "interleaved":
+                    _Scheduler(self, [(mb, "both") for mb in range(num_mb)], window).run()
+                else:           # simple: every forward, then every backward; _only_forward: forwards only
+                    _Scheduler(self, [(mb, "fwd") for mb in range(num_mb)], window).run()
+                    _Scheduler(self, [(mb, "bwd") for mb in range(num_mb) if mb in self.deferred_bwd], window).run()
                 outputs = self._step_ctx["outputs"]
             finally:
                 self._step_ctx = None

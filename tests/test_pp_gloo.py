@@ -61,3 +61,65 @@ def test_pp2_matches_dense(pipeline):
         assert r["ranks_used"] == [0, 1]
         assert r["n_local"] > 0
     assert sum(r["n_local"] for r in res) > 0
+
+
+def _pp_tp_worker(rank, world, window):
+    """pp=2 x tp=2 on four processes.  Exercises the deterministic leader schedule: all tp ranks of a stage must
+    issue their collectives in the same order."""
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"pipeline_parallel_degree": 2, "tensor_parallel_degree": 2, "microbatches": 4, "ddp": True,
+              "active_microbatches": window, "ddp_dist_backend": "gloo"})
+    torch.manual_seed(7)
+    with smp.tensor_parallelism(enabled=True):
+        module = smp.nn.DistributedTransformerLMHead(**CFG)
+    model = smp.DistributedModel(module)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    @smp.step
+    def eval_step(model, ids):
+        return model((ids, None, None, None, ids))[0]
+
+    torch.manual_seed(11)
+    all_ids = torch.randint(0, CFG["vocab_size"], (3, 16, 16))
+    with torch.no_grad():
+        eval_step(model, all_ids[0, :8])          # partitions the model
+    full = {k: v.clone() for k, v in model.state_dict().items()}
+    losses = []
+    for it in range(3):
+        ids = all_ids[it, smp.tp_rank() * 8:(smp.tp_rank() + 1) * 8]
+        opt.zero_grad()
+        out = train_step(model, ids)
+        opt.step()
+        losses.append(out.reduce_mean().item())
+    return {"losses": losses, "full": full, "tp_rank": smp.tp_rank(), "pp_rank": smp.pp_rank(), "rank": rank}
+
+
+@pytest.mark.parametrize("window", [2, 4])
+def test_pp2_tp2_tracks_dense(window):
+    """Several optimizer steps must track the dense model (built here, tp=1) trained on the union of the
+    tensor-parallel ranks' batches - every tp rank brings its own sequences."""
+    res = run_distributed(_pp_tp_worker, 4, window, timeout=420)
+    import smdistributed_modelparallel_b200  # noqa: F401
+    from smdistributed_modelparallel_b200.nn.transformer import DistributedTransformerLMHead
+
+    dense = DistributedTransformerLMHead(**CFG)
+    r0 = next(r for r in res if r["rank"] == 0)
+    missing = dense.load_state_dict(r0["full"], strict=False)
+    assert not [k for k in missing.missing_keys if "lm_head" not in k], missing
+    oopt = torch.optim.SGD(dense.parameters(), lr=0.1)
+    torch.manual_seed(11)
+    all_ids = torch.randint(0, CFG["vocab_size"], (3, 16, 16))
+    for it in range(3):
+        oopt.zero_grad()
+        ol, _ = dense((all_ids[it], None, None, None, all_ids[it]))
+        ol.backward()
+        oopt.step()
+        mean = sum(r["losses"][it] for r in res if r["pp_rank"] == 0) / 2
+        assert abs(mean - ol.item()) < 2e-4, (it, mean, ol.item())
