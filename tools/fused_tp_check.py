@@ -74,8 +74,16 @@ def timeit(fn, iters=10):
 
 
 # GPT-J 6B shapes at micro-batch 4 x 2048 tokens per tp group
-T, H = 8192, 4096
+T, H = int(os.environ.get("TP_CHECK_T", 8192)), int(os.environ.get("TP_CHECK_H", 4096))
 T_l = T // n
+log(f"shapes: T={T} H={H} tp={n}")
+
+
+def roof(t_gemm, nbytes):
+    """Roofline of a fused GEMM+collective: the slower of the GEMM alone and its bytes over NVLink at 900 GB/s."""
+    return max(t_gemm, nbytes / 900e9 * 1e3)
+
+
 for name, K, N in [("qkv+mlp1 (AG->GEMM)", H, (3 * H + 4 * H) // n), ("qkv (AG->GEMM)", H, 3 * H // n)]:
     x = torch.randn(T_l, K, device=dev, dtype=bf); w = torch.randn(N, K, device=dev, dtype=bf) * 0.02
     t_f = timeit(lambda: m.ag_gemm(x, w))
@@ -83,7 +91,8 @@ for name, K, N in [("qkv+mlp1 (AG->GEMM)", H, (3 * H + 4 * H) // n), ("qkv (AG->
     t_g = timeit(lambda: gemm(torch.empty(T, K, device=dev, dtype=bf), w))
     t_c = timeit(lambda: tp_ops.gather_tokens(x, g))
     fl = 2.0 * T * N * K
-    log(f"{name}: fused {t_f:.3f} ms ({fl/t_f/1e9:.0f} TF) | nccl AG + gemm {t_n:.3f} ms | gemm alone {t_g:.3f} | AG alone {t_c:.3f}")
+    rf = roof(t_g, T * K * 2 * (n - 1) / n)
+    log(f"{name}: fused {t_f:.3f} ms ({fl/t_f/1e9:.0f} TF) | nccl AG + gemm {t_n:.3f} ms | gemm alone {t_g:.3f} | AG alone {t_c:.3f} | roofline {rf:.3f} ms -> {100 * rf / t_f:.0f} %")
 for name, K, N in [("mlp2 (GEMM->RS)", 4 * H // n, H), ("attn dense (GEMM->RS)", H // n, H)]:
     x = torch.randn(T, K, device=dev, dtype=bf); w = torch.randn(N, K, device=dev, dtype=bf) * 0.02
     t_f = timeit(lambda: m.gemm_rs(x, w))
@@ -92,5 +101,6 @@ for name, K, N in [("mlp2 (GEMM->RS)", 4 * H // n, H), ("attn dense (GEMM->RS)",
     y = gemm(x, w)
     t_c = timeit(lambda: tp_ops.scatter_sum_tokens(y, g))
     fl = 2.0 * T * N * K
-    log(f"{name}: fused {t_f:.3f} ms ({fl/t_f/1e9:.0f} TF) | gemm + nccl RS {t_n:.3f} ms | gemm alone {t_g:.3f} | RS alone {t_c:.3f}")
+    rf = roof(t_g, T * N * 2 * (n - 1) / n)
+    log(f"{name}: fused {t_f:.3f} ms ({fl/t_f/1e9:.0f} TF) | gemm + nccl RS {t_n:.3f} ms | gemm alone {t_g:.3f} | RS alone {t_c:.3f} | roofline {rf:.3f} ms -> {100 * rf / t_f:.0f} %")
 dist.barrier()
