@@ -173,6 +173,9 @@ class DistributedModel(nn.Module):
                 self._broadcast_parameters_and_buffers()
                 self.reducer = GradReducer(params, state.rdp_process_group, state.dp_process_group, core.dp_size(),
                                            self.bucket_cap_mb, self.grad_buffer)
+                if self.overlapping_allreduce and not cfg.shard_optimizer_state:
+                    self.reducer.install_overlap(
+                        self.module, lambda: state.microbatch == state.num_microbatches() - 1)
         from .runtime.checkpointing import apply_configured_checkpointing
         apply_configured_checkpointing(self.module)
         for hook in list(self._post_partition_hooks.values()):

@@ -278,7 +278,20 @@ def _all_to_all_impl(x, split_dim, merge_dim, split_shapes=None, merge_shapes=No
         shp[split_dim] = s_shapes[r]
         shp[merge_dim] = merge_shapes[k]
         recvs.append(torch.empty(shp, dtype=x.dtype, device=x.device))
-    _throttled(dist.all_to_all, recvs, sends, group=group)
+    if x.is_cuda:
+        _throttled(dist.all_to_all, recvs, sends, group=group)
+    else:
+        # gloo has no list all-to-all: pairwise exchange (the reference's CPU path is point-to-point too,
+        # reference torch/collectives.py:247-318)
+        recvs[r].copy_(sends[r])
+        ops = []
+        for k in range(n):
+            if k != r:
+                peer = dist.get_global_rank(group, k)
+                ops.append(dist.P2POp(dist.isend, sends[k], peer, group))
+                ops.append(dist.P2POp(dist.irecv, recvs[k], peer, group))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
     return torch.cat(recvs, dim=merge_dim)
 
 

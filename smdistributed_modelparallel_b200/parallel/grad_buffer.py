@@ -96,7 +96,15 @@ def _allreduce_sliced(flat: torch.Tensor, group, scale: float, bucket_elems: int
 
 
 class GradReducer:
-    """Data-parallel reduction of a GradBuffer (or of plain ``.grad`` tensors in fp32 training)."""
+    """Data-parallel reduction of a GradBuffer (or of plain ``.grad`` tensors in fp32 training).
+
+    With a GradBuffer the all-reduce is overlapped with backward: ``install_overlap`` makes every sizeable
+    child of an ``nn.Sequential`` / ``nn.ModuleList`` (a transformer layer) a bucket - its parameters occupy
+    one contiguous slice per buffer region - and marks the child's inputs (parallel/boundary.py); when the last
+    microbatch's backward leaves the child, the bucket's slices are all-reduced asynchronously on NCCL's
+    stream while the layers before it are still differentiating.  Whatever no bucket covers (embeddings,
+    final norm, shared parameters) is reduced in ``synchronize``.  Replaces the reference's native bucketed
+    reducer (reference torch/ddp_model.py:336-374; bucket cap argument kept)."""
 
     def __init__(self, model_params, rdp_group, dp_group, dp_size, bucket_cap_mb=100, grad_buffer: GradBuffer | None = None):
         self.rdp_group, self.dp_group = rdp_group, dp_group
@@ -106,9 +114,98 @@ class GradReducer:
         self.params = [p for p in model_params if p.requires_grad]
         self.comm_hook = None
         self.require_sync = True
+        self.buckets = []             # [{"ranges": [(region, a, b)], "module": m}]
+        self._launched = []           # (region, a, b, work) for this step
+        self._hooks = []
+        self.is_last_microbatch = lambda: True
+        self.stats = {"overlapped_elems": 0, "tail_elems": 0}
 
     def register_comm_hook(self, state, hook):
         self.comm_hook = (state, hook)
+
+    # ------------------------------------------------------------------ overlap
+    def install_overlap(self, root, is_last_microbatch, min_elems=None):
+        """Create per-layer buckets under ``root`` and hook their inputs."""
+        import os
+
+        import torch.nn as nn
+
+        if min_elems is None:
+            min_elems = int(os.environ.get("SMP_DDP_BUCKET_MIN_ELEMS", 1 << 18))
+
+        from .boundary import mark_inputs
+
+        gb = self.grad_buffer
+        if gb is None or self.dp_size == 1:
+            return 0
+        self.is_last_microbatch = is_last_microbatch
+        use_count = {}
+        for m in root.modules():
+            for p in m.parameters(recurse=False):
+                use_count[p] = use_count.get(p, 0) + 1
+        padded = lambda p: (p.numel() + 7) // 8 * 8          # noqa: E731 - layout rule of GradBuffer
+        for container in root.modules():
+            if not isinstance(container, (nn.Sequential, nn.ModuleList)):
+                continue
+            for child in container.children():
+                plist = [p for p in child.parameters() if p in gb.offsets]
+                if not plist or sum(p.numel() for p in plist) < min_elems or any(use_count.get(p, 1) > 1 for p in plist):
+                    continue
+                ranges = []
+                for region, (ra, rb) in gb.regions.items():
+                    ps = [p for p in plist if ra <= gb.offsets[p] < rb]
+                    if not ps:
+                        continue
+                    a = min(gb.offsets[p] for p in ps)
+                    b = max(gb.offsets[p] + padded(p) for p in ps)
+                    if sum(padded(p) for p in ps) != b - a:       # not contiguous: leave it to synchronize()
+                        ranges = None
+                        break
+                    ranges.append((region, a, min(b, rb)))
+                if not ranges:
+                    continue
+                idx = len(self.buckets)
+                self.buckets.append({"ranges": ranges, "module": child})
+                self._hooks.append(child.register_forward_pre_hook(
+                    lambda mod, args, _i=idx: mark_inputs(args, lambda: self._bucket_ready(_i))))
+        return len(self.buckets)
+
+    def _group_of(self, region):
+        return self.rdp_group if region == "scaled_batch" else self.dp_group
+
+    def _bucket_ready(self, idx):
+        if not self.require_sync or not self.is_last_microbatch() or self.comm_hook is not None:
+            return
+        buf = self.grad_buffer.buffer
+        for region, a, b in self.buckets[idx]["ranges"]:
+            group = self._group_of(region)
+            if group is None or dist.get_world_size(group) == 1:
+                continue
+            if any(r == region and a < hb and la < b for r, la, hb, _ in self._launched):
+                continue                                   # already on its way (module ran twice)
+            work = dist.all_reduce(buf[a:b], group=group, async_op=True)
+            self._launched.append((region, a, b, work))
+            self.stats["overlapped_elems"] += b - a
+
+    def _finish_overlapped(self):
+        """Wait for the in-flight buckets, reduce what they did not cover."""
+        gb = self.grad_buffer
+        launched, self._launched = self._launched, []
+        for _, _, _, work in launched:
+            work.wait()
+        for region, (ra, rb) in gb.regions.items():
+            group = self._group_of(region)
+            if group is None or dist.get_world_size(group) == 1:
+                continue
+            done = sorted((a, b) for r, a, b, _ in launched if r == region)
+            cur = ra
+            for a, b in done + [(rb, rb)]:
+                if a > cur:
+                    n = a - cur
+                    for s in range(cur, a, self.bucket_elems):
+                        dist.all_reduce(gb.buffer[s:min(a, s + self.bucket_elems)], group=group)
+                    self.stats["tail_elems"] += n
+                cur = max(cur, b)
 
     def synchronize(self):
         """All-reduce every gradient: scaled-batch parameters over the RDP group, the rest over the DP
@@ -117,8 +214,12 @@ class GradReducer:
             return
         scale = 1.0 / self.dp_size
         if self.grad_buffer is not None:
-            _allreduce_sliced(self.grad_buffer.region("scaled_batch"), self.rdp_group, scale, self.bucket_elems)
-            _allreduce_sliced(self.grad_buffer.region("default"), self.dp_group, scale, self.bucket_elems)
+            if self.comm_hook is not None:
+                _allreduce_sliced(self.grad_buffer.region("scaled_batch"), self.rdp_group, scale, self.bucket_elems)
+                _allreduce_sliced(self.grad_buffer.region("default"), self.dp_group, scale, self.bucket_elems)
+                return
+            self._finish_overlapped()
+            self.grad_buffer.buffer.mul_(scale)
             return
         for want_scaled, group in ((True, self.rdp_group), (False, self.dp_group)):
             grads = [p.grad for p in self.params if p.grad is not None and is_scaled_batch_parameter(p) == want_scaled]

@@ -35,6 +35,7 @@ from ..backend.exceptions import SMPValidationError, UnsupportedShardedConfigErr
 from ..backend.logger import get_logger
 from ..ops import multi_tensor as MT
 from ..precision.loss_scaler import DynamicLossScaler, LossScaler
+from .boundary import mark_inputs
 from .grad_buffer import GradBuffer
 
 
@@ -96,36 +97,6 @@ class Unit:
         """This rank's (or ``rank``'s) elements of a full-unit tensor, in shard order."""
         r = self.rank if rank is None else rank
         return full.view(self.ppr, self.degree, self.piece)[:, r].reshape(-1)
-
-
-def _map_tensors(obj, fn):
-    if torch.is_tensor(obj):
-        return fn(obj)
-    if isinstance(obj, tuple):
-        return tuple(_map_tensors(o, fn) for o in obj)
-    if isinstance(obj, list):
-        return [_map_tensors(o, fn) for o in obj]
-    if isinstance(obj, dict):
-        return {k: _map_tensors(v, fn) for k, v in obj.items()}
-    return obj
-
-
-class _UnitBoundary(torch.autograd.Function):
-    """Identity on a unit's (differentiable) inputs.  Its backward runs after every other node of the unit -
-    all weight gradients of the unit are final - so that is where the unit's reduce-scatter is issued.  (Module
-    full-backward hooks cannot do this: they only see top-level tensor arguments, and the transformer layers take
-    one tuple.)"""
-
-    @staticmethod
-    def forward(ctx, engine, units, *tensors):
-        ctx.engine, ctx.units = engine, units
-        return tuple(t.view_as(t) for t in tensors)
-
-    @staticmethod
-    def backward(ctx, *grads):
-        for u in ctx.units:
-            ctx.engine._reduce_unit(u)
-        return (None, None) + grads
 
 
 class ShardedDataParallelEngine:
@@ -316,14 +287,12 @@ class ShardedDataParallelEngine:
             u.users += 1
         if not self._in_backward:            # a recomputed forward must not prefetch units that are already done
             self._prefetch_after(units[-1], +1)
-        if args is None or not torch.is_grad_enabled():
+        if args is None:
             return None
-        found = []
-        _map_tensors(args, lambda t: found.append(t) if t.requires_grad else None)
-        if not found:
-            return None                      # nothing to hang the boundary on: flushed at the end of backward
-        outs = iter(_UnitBoundary.apply(self, units, *found))
-        return _map_tensors(args, lambda t: next(outs) if t.requires_grad else t)
+        # the marker's backward runs after every other node of the unit: all its weight gradients are final,
+        # so that is where the unit's reduce-scatter is issued (None when there is nothing to hang it on: such
+        # units are flushed at the end of backward)
+        return mark_inputs(args, lambda _us=tuple(units): [self._reduce_unit(u) for u in _us])
 
     def _post_forward(self, units):
         for u in units:

@@ -18,6 +18,9 @@ def _dp_worker(rank, world, shard, bf16):
 
     import smdistributed_modelparallel_b200 as smp
 
+    import os
+
+    os.environ["SMP_DDP_BUCKET_MIN_ELEMS"] = "1000"          # the toy layers become all-reduce buckets
     smp.init({"ddp": True, "microbatches": 2, "shard_optimizer_state": shard, "bf16": bf16})
     torch.manual_seed(3)
     module = smp.nn.DistributedTransformerLMHead(**CFG)
@@ -46,7 +49,8 @@ def _dp_worker(rank, world, shard, bf16):
         ol.backward()
         oopt.step()
     worst = max((a.float() - b).abs().max().item() for a, b in zip(model.module.parameters(), oracle.parameters()))
-    return {"worst": worst, "losses": losses}
+    stats = dict(model.reducer.stats) if model.reducer is not None else {}
+    return {"worst": worst, "losses": losses, "stats": stats, "buckets": len(getattr(model.reducer, "buckets", []))}
 
 
 @pytest.mark.parametrize("shard,bf16", [(False, False), (True, False), (True, True), (False, True)])
@@ -55,6 +59,9 @@ def test_dp2_matches_dense(shard, bf16):
     tol = 4e-3 if not bf16 else 5e-2
     for r in res:
         assert r["worst"] < tol, r
+        if bf16 and not shard:
+            # 16-bit training without optimizer-state sharding: the two layers are reduced while backward runs
+            assert r["buckets"] == 2 and r["stats"]["overlapped_elems"] > 0 and r["stats"]["tail_elems"] > 0, r
     assert abs(res[0]["worst"] - res[1]["worst"]) < 1e-6 or bf16
 
 
