@@ -95,25 +95,28 @@ struct GemmParams {
   uint32_t idesc;
 };
 
-template <int BN>
+// CTA2: the tile is computed by a CTA pair (cta_group::2): 256 x BN output, each CTA holds its 128 rows of A and
+// half of the B rows per stage, so a stage is 32 KB instead of 48 KB and six stages fit.
+template <int BN, bool CTA2 = false>
 struct Cfg {
   static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
-  static constexpr int B_BYTES = BN * BLOCK_K * 2;
+  static constexpr int B_ROWS = CTA2 ? BN / 2 : BN;
+  static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int STAGES = CTA2 ? 6 : ((BN == 256) ? 4 : (BN == 128 ? 6 : 8));
   static constexpr int TMEM_COLS = 2 * BN;  // double-buffered accumulator (power of two >= 32)
   static constexpr int EPI_STAGE_BYTES = 4 * 32 * 256;  // per epilogue warp: 32 rows x 256 B, for coalesced stores
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-__device__ __forceinline__ void tile_coords(int t, const GemmParams& p, int& b, int& m_blk, int& n_blk) {
-  const int per_batch = p.num_m * p.num_n;
+__device__ __forceinline__ void tile_coords(int t, const GemmParams& p, int num_m, int& b, int& m_blk, int& n_blk) {
+  const int per_batch = num_m * p.num_n;
   b = t / per_batch;
   const int r = t - b * per_batch;
   const int group_size = GROUP_M * p.num_n;
   const int group_id = r / group_size;
   const int first_m = group_id * GROUP_M;
-  const int gsm = min(p.num_m - first_m, GROUP_M);
+  const int gsm = min(num_m - first_m, GROUP_M);
   const int in_group = r - group_id * group_size;
   m_blk = first_m + in_group % gsm;
   n_blk = in_group / gsm;
@@ -209,11 +212,14 @@ __device__ __forceinline__ void store32_dyn(void* base, int dtype, long long off
     store32<__half>(reinterpret_cast<__half*>(base) + off, v, vec, nvalid);
 }
 
-template <int BN>
+template <int BN, bool CTA2>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                         const GemmParams p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, CTA2>;
+  // CTA pair: rank 0 (leader) issues the MMAs for both; each CTA loads, and later stores, its own 128 rows
+  const int cta_rank = CTA2 ? (int)cluster_ctarank() : 0;
+  const bool leader = cta_rank == 0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* epi_stage = smem + C::STAGES * C::STAGE_BYTES;
@@ -238,22 +244,30 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], 4);  // one arrive per epilogue warp
+      mbar_init(&tempty_bar[i], CTA2 ? 8 : 4);  // one arrive per epilogue warp (of both CTAs of a pair)
     }
     fence_mbar_init();
+    if (CTA2) fence_mbar_init_cluster();
   }
   if (warp == 2) {
-    tmem_alloc<C::TMEM_COLS>(tmem_slot);
-    tmem_relinquish();
+    if (CTA2) {
+      tmem_alloc_2sm<C::TMEM_COLS>(tmem_slot);
+      tmem_relinquish_2sm();
+    } else {
+      tmem_alloc<C::TMEM_COLS>(tmem_slot);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if (CTA2) cluster_sync_all();  // the peer's barriers are initialised before anything is signalled across CTAs
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int total_tiles = p.batch * p.num_m * p.num_n;
-  const int tile0 = (int)blockIdx.x;
-  const int tstride = (int)gridDim.x;
+  const int num_m_eff = CTA2 ? (p.num_m + 1) / 2 : p.num_m;  // pair tiles span two 128-row blocks
+  const int total_tiles = p.batch * num_m_eff * p.num_n;
+  const int tile0 = CTA2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tstride = CTA2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0) {
     // ===================================================================== TMA producer
@@ -262,9 +276,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       uint32_t phase = 0;
       for (int t = tile0; t < total_tiles; t += tstride) {
         int b, m_blk, n_blk;
-        tile_coords(t, p, b, m_blk, n_blk);
-        m_blk = permute_m_block(m_blk, p);
+        tile_coords(t, p, num_m_eff, b, m_blk, n_blk);
+        m_blk = CTA2 ? m_blk * 2 + cta_rank : permute_m_block(m_blk, p);
         const int m0 = m_blk * BLOCK_M, n0 = n_blk * BN;
+        const int nb0 = n0 + cta_rank * C::B_ROWS;  // this CTA's share of the B rows (all of them without pairing)
         if (p.comm.mode == COMM_AG && m0 / p.comm.rows_per_rank != p.comm.rank) {
           // rows of a remote shard: wait until a copy CTA has landed this 128-row block, then make the
           // generic-proxy writes visible to the TMA (async proxy) reads that follow
@@ -281,21 +296,27 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
           uint8_t* sb = sa + C::A_BYTES;
-          mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+          if (leader) mbar_expect_tx(&full_bar[stage], (CTA2 ? 2 : 1) * C::STAGE_BYTES);
           const int k0 = kb * BLOCK_K;
           if (!p.a_mn_major) {
-            tma_load_3d(sa, &tma_a, &full_bar[stage], k0, m0, b);
+            if (CTA2) tma_load_3d_2sm(sa, &tma_a, &full_bar[stage], k0, m0, b);
+            else tma_load_3d(sa, &tma_a, &full_bar[stage], k0, m0, b);
           } else {
 #pragma unroll
-            for (int j = 0; j < BLOCK_M / 64; ++j)
-              tma_load_3d(sa + j * (BLOCK_K * 128), &tma_a, &full_bar[stage], m0 + j * 64, k0, b);
+            for (int j = 0; j < BLOCK_M / 64; ++j) {
+              if (CTA2) tma_load_3d_2sm(sa + j * (BLOCK_K * 128), &tma_a, &full_bar[stage], m0 + j * 64, k0, b);
+              else tma_load_3d(sa + j * (BLOCK_K * 128), &tma_a, &full_bar[stage], m0 + j * 64, k0, b);
+            }
           }
           if (!p.b_mn_major) {
-            tma_load_3d(sb, &tma_b, &full_bar[stage], k0, n0, b);
+            if (CTA2) tma_load_3d_2sm(sb, &tma_b, &full_bar[stage], k0, nb0, b);
+            else tma_load_3d(sb, &tma_b, &full_bar[stage], k0, nb0, b);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_3d(sb + j * (BLOCK_K * 128), &tma_b, &full_bar[stage], n0 + j * 64, k0, b);
+            for (int j = 0; j < C::B_ROWS / 64; ++j) {
+              if (CTA2) tma_load_3d_2sm(sb + j * (BLOCK_K * 128), &tma_b, &full_bar[stage], nb0 + j * 64, k0, b);
+              else tma_load_3d(sb + j * (BLOCK_K * 128), &tma_b, &full_bar[stage], nb0 + j * 64, k0, b);
+            }
           }
           if (++stage == C::STAGES) {
             stage = 0;
@@ -305,8 +326,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       }
     }
   } else if (warp == 1) {
-    // ===================================================================== MMA issuer
-    if (lane == 0) {
+    // ===================================================================== MMA issuer (pair: leader CTA only)
+    if (lane == 0 && leader) {
       // K-major: 8-row groups 1024 B apart.  MN-major: K rows 128 B apart inside a 64-wide atom,
       // 8-row groups 1024 B apart, atoms BLOCK_K*128 B apart.
       const uint64_t hi_a = p.a_mn_major ? make_smem_desc_hi(BLOCK_K * 128, 1024) : make_smem_desc_hi(16, 1024);
@@ -331,15 +352,20 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           const uint64_t db = make_smem_desc(sb, hi_b);
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            umma_f16(tmem_d, da + uint64_t(k * adv_a), db + uint64_t(k * adv_b), p.idesc, (kb | k) != 0);
+            if (CTA2) umma_f16_2sm(tmem_d, da + uint64_t(k * adv_a), db + uint64_t(k * adv_b), p.idesc, (kb | k) != 0);
+            else umma_f16(tmem_d, da + uint64_t(k * adv_a), db + uint64_t(k * adv_b), p.idesc, (kb | k) != 0);
           }
-          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          // frees the smem slot (in both CTAs of a pair) once these MMAs retire
+          if (CTA2) umma_commit_2sm(&empty_bar[stage]);
+          else umma_commit(&empty_bar[stage]);
           if (++stage == C::STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue warps (of both CTAs)
+        if (CTA2) umma_commit_2sm(&tfull_bar[acc]);
+        else umma_commit(&tfull_bar[acc]);
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -446,8 +472,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     (void)b_es;
     for (int t = tile0; t < total_tiles; t += tstride) {
       int b, m_blk, n_blk;
-      tile_coords(t, p, b, m_blk, n_blk);
-      m_blk = permute_m_block(m_blk, p);
+      tile_coords(t, p, num_m_eff, b, m_blk, n_blk);
+      m_blk = CTA2 ? m_blk * 2 + cta_rank : permute_m_block(m_blk, p);
       const int row = m_blk * BLOCK_M + ew * 32 + lane;
       const int n0 = n_blk * BN;
       // reduce-scatter: this tile's rows belong to rank `dest`; write into its staging slot for this rank
@@ -460,7 +486,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         row_in_c = (long long)p.comm.rank * p.comm.rows_per_rank + (row - (long long)dest * p.comm.rows_per_rank);
       }
       // whole tile in range and a 16-bit output: stage through shared memory for coalesced row stores
-      const bool staged = p.comm.mode == COMM_RS && out_es == 2 && c_vec_ok && (m_blk * BLOCK_M + BLOCK_M <= p.M) && (n0 + BN <= p.N);
+      // (always for reduce-scatter; for plain GEMMs only when the reduction is short - QK^T-like, store-bound
+      // tiles - because the extra shared-memory pass costs ~3 % on compute-bound ones)
+      const bool staged = (p.comm.mode == COMM_RS || (p.K <= 512 && p.aux == nullptr)) && out_es == 2 && c_vec_ok &&
+                          (m_blk * BLOCK_M + BLOCK_M <= p.M) && (n0 + BN <= p.N);
       uint8_t* wstage = epi_stage + ew * (32 * 256);
       const long long row_in_c0 = row_in_c - lane;
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -567,7 +596,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       // all TMEM reads of this accumulator stage are done -> hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) {
+        if (CTA2) mbar_arrive_leader(&tempty_bar[acc]);
+        else mbar_arrive(&tempty_bar[acc]);
+      }
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
@@ -577,9 +609,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 
   tc_fence_before();
   __syncthreads();
+  if (CTA2) cluster_sync_all();  // the peer may still be reading this CTA's shared memory / TMEM until here
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc<C::TMEM_COLS>(tmem_base);
+    if (CTA2) tmem_dealloc_2sm<C::TMEM_COLS>(tmem_base);
+    else tmem_dealloc<C::TMEM_COLS>(tmem_base);
   }
 }
 
@@ -635,22 +669,43 @@ int make_operand_map(CUtensorMap* map, int in_dtype, const void* ptr, int rows, 
   return 0;
 }
 
-template <int BN>
+template <int BN, bool CTA2>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStream_t stream, int max_ctas) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, CTA2>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    SMPK_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SMPK_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, CTA2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          C::SMEM_BYTES));
     attr_set[dev & 63] = true;
   }
   p.num_n = (p.N + BN - 1) / BN;
-  p.idesc = make_idesc_f16(/*fmt filled by caller in idesc low bits*/ p.idesc, p.a_mn_major, p.b_mn_major, BLOCK_M, BN);
-  const int total = p.batch * p.num_m * p.num_n;
+  p.idesc = make_idesc_f16(/*fmt filled by caller in idesc low bits*/ p.idesc, p.a_mn_major, p.b_mn_major,
+                           CTA2 ? 2 * BLOCK_M : BLOCK_M, BN);
+  const int num_m_eff = CTA2 ? (p.num_m + 1) / 2 : p.num_m;
+  const int total = p.batch * num_m_eff * p.num_n;
   int grid = smpk::num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (CTA2) {
+    grid &= ~1;                                  // whole pairs
+    if (2 * total < grid) grid = 2 * total;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = C::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    SMPK_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, CTA2>, ta, tb, p));
+    return 0;
+  }
   if (total < grid) grid = total;
   if (p.comm.mode == COMM_AG) {
     // arrival counters of the row blocks start at zero for this launch
@@ -663,9 +718,20 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStre
     const size_t nblk = (size_t)((p.comm.total_rows + BN - 1) / BN);
     SMPK_CHECK_CUDA(cudaMemsetAsync(p.comm.blk_flags, 0, sizeof(uint32_t) * nblk, stream));
   }
-  gemm_tcgen05_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+  gemm_tcgen05_kernel<BN, CTA2><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
   SMPK_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+// Pairing (cta_group::2): 0 = never, 1 = when the problem is large enough (default), 2 = whenever it applies
+// (tests).  SMPK_GEMM_2CTA sets the initial value; smpk_gemm_set_pair_mode changes it at run time.
+int g_pair_mode = -1;
+int pair_mode() {
+  if (g_pair_mode < 0) {
+    const char* e = getenv("SMPK_GEMM_2CTA");
+    g_pair_mode = (e == nullptr) ? 1 : (e[0] == '0' ? 0 : (e[0] == '2' ? 2 : 1));
+  }
+  return g_pair_mode;
 }
 
 }  // namespace
@@ -689,6 +755,12 @@ static int gemm_impl(void* stream, int in_dtype, int out_dtype, int M, int N, in
                      int b_mn_major, void* C, int ldc, long long c_bs, const void* bias, int bias_dtype,
                      const void* R, int ldr, long long r_bs, int r_dtype, void* aux, float alpha, float beta,
                      int epi, int max_ctas, const SmpkCommDesc* comm);
+
+SMPK_API int smpk_gemm_set_pair_mode(int mode) {
+  const int old = pair_mode();
+  if (mode >= 0 && mode <= 2) g_pair_mode = mode;
+  return old;
+}
 
 // See include/smpb200_kernels.h for the contract.
 SMPK_API int smpk_gemm(void* stream, int in_dtype, int out_dtype, int M, int N, int K, int batch, const void* A,
@@ -766,13 +838,19 @@ static int gemm_impl(void* stream, int in_dtype, int out_dtype, int M, int N, in
   }
 
   const int BN = (N > 128) ? 256 : (N > 64 ? 128 : 64);
+  // CTA pairs for plain GEMMs with enough 256 x 256 tiles to occupy every pair; fused-collective modes and small
+  // problems stay on single CTAs
+  const long long pair_tiles = (long long)batch * ((p.num_m + 1) / 2) * ((N + 255) / 256);
+  const int pm = pair_mode();
+  const bool pair = BN == 256 && comm == nullptr && M > BLOCK_M && pm > 0 && (pm == 2 || pair_tiles >= smpk::num_sms() / 4);
   CUtensorMap ta, tb;
   int rc = make_operand_map(&ta, in_dtype, A, M, K, batch, lda, a_bs, p.a_mn_major, BLOCK_M);
   if (rc) return rc;
-  rc = make_operand_map(&tb, in_dtype, B, N, K, batch, ldb, b_bs, p.b_mn_major, BN);
+  rc = make_operand_map(&tb, in_dtype, B, N, K, batch, ldb, b_bs, p.b_mn_major, pair ? BN / 2 : BN);
   if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  if (BN == 256) return launch<256>(ta, tb, p, s, max_ctas);
-  if (BN == 128) return launch<128>(ta, tb, p, s, max_ctas);
-  return launch<64>(ta, tb, p, s, max_ctas);
+  if (pair) return launch<256, true>(ta, tb, p, s, max_ctas);
+  if (BN == 256) return launch<256, false>(ta, tb, p, s, max_ctas);
+  if (BN == 128) return launch<128, false>(ta, tb, p, s, max_ctas);
+  return launch<64, false>(ta, tb, p, s, max_ctas);
 }

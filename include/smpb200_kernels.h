@@ -61,6 +61,9 @@ int smpk_gemm_comm(void* stream, int in_dtype, int out_dtype, int M, int N, int 
                    int a_mn_major, const void* B, int ldb, int b_mn_major, void* C, int ldc, const void* bias,
                    int bias_dtype, const void* R, int ldr, int r_dtype, float beta, void* aux, float alpha, int epi,
                    int max_ctas, const SmpkCommDesc* comm);
+/* CTA-pair (tcgen05 cta_group::2, 256 x 256 tiles over the two SMs of a TPC) policy of smpk_gemm: 0 never, 1 when the
+ * problem has enough pair tiles (default), 2 whenever N > 128 and M > 128.  Returns the previous mode. */
+int smpk_gemm_set_pair_mode(int mode);
 int smpk_flags_signal(void* stream, void* const* peer_flags, int n, int index, unsigned int value);
 int smpk_flags_wait(void* stream, const void* flags, int n, int skip, unsigned int value);
 int smpk_p2p_allgather(void* stream, void* const* peer_src, void* local_buf, long long slot_bytes,

@@ -31,6 +31,11 @@ from ._sdp_hook import pending_gathers as _sdp_pending  # noqa: E402
 _max_ctas = 0
 
 
+def set_pair_mode(mode: int) -> int:
+    """CTA-pair (cta_group::2) policy of the GEMM kernel: 0 never, 1 automatic, 2 whenever applicable."""
+    return N.query("smpk_gemm_set_pair_mode", int(mode))
+
+
 def set_max_ctas(n: int) -> None:
     global _max_ctas
     _max_ctas = int(n)

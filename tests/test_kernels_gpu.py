@@ -66,6 +66,42 @@ def test_gemm_layouts(M, N, K, layout, dtype):
     _report(f"gemm {layout}", out, ref, 1e-2)
 
 
+PAIR_SHAPES = [(256, 256, 64), (512, 512, 256), (384, 640, 96), (1000, 520, 328), (2048, 1024, 512), (130, 264, 72)]
+
+
+@pytest.mark.parametrize("M,N,K", PAIR_SHAPES)
+@pytest.mark.parametrize("layout", ["nt", "nn", "tn"])
+def test_gemm_cta_pair(M, N, K, layout):
+    """cta_group::2 path (256 x 256 tiles over a CTA pair) forced on small shapes: odd block counts, partial
+    tiles in M, N and K, every operand layout, plain / batched / accumulate-into-fp32 outputs."""
+    from smdistributed_modelparallel_b200.ops.gemm import gemm, set_pair_mode
+
+    torch.manual_seed(M + N + K)
+    A = torch.randn(3, M, K, device=DEV, dtype=torch.bfloat16)
+    B = torch.randn(3, N, K, device=DEV, dtype=torch.bfloat16)
+    ref = torch.matmul(A.float(), B.float().transpose(-1, -2))
+    old = set_pair_mode(2)
+    try:
+        def run(a, b):
+            if layout == "nt":
+                return gemm(a, b)
+            if layout == "nn":
+                return gemm(a, b.transpose(-1, -2).contiguous(), b_mn_major=True)
+            return gemm(a.transpose(-1, -2).contiguous(), b.transpose(-1, -2).contiguous(), a_mn_major=True,
+                        b_mn_major=True)
+
+        out2 = run(A[0], B[0])
+        out3 = run(A, B)
+        acc = torch.ones(M, N, device=DEV, dtype=torch.float32)
+        gemm(A[1], B[1], out=acc, residual=acc, beta=1.0)
+        torch.cuda.synchronize()
+    finally:
+        set_pair_mode(old)
+    _report(f"pair gemm {layout}", out2, ref[0], 1e-2)
+    _report(f"pair gemm batched {layout}", out3, ref, 1e-2)
+    _report(f"pair gemm accumulate {layout}", acc, ref[1] + 1.0, 1e-2)
+
+
 @pytest.mark.parametrize("epi", ["none", "gelu_tanh", "gelu_erf"])
 def test_gemm_epilogues(epi):
     from smdistributed_modelparallel_b200.ops.gemm import gemm
