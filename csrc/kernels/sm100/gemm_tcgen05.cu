@@ -92,8 +92,38 @@ struct GemmParams {
   int bias_dtype;
   float alpha, beta;
   int epi;
+  // causal structure (square attention problems, M == N or M == K): 0 none;
+  //   1: only output tiles that touch the lower triangle (n0 < tile row end) are computed - QK^T, dO V^T;
+  //   2: A is lower triangular [M, K]: the reduction stops at the tile's last row - P V, dS K;
+  //   3: A^T is lower triangular (A given MN-major [K, M]): the reduction starts at the tile's first row - P^T dO, dS^T Q
+  int tri;
   uint32_t idesc;
 };
+
+// Rows covered by the tile that m_blk belongs to (a CTA pair covers two 128-row blocks).
+template <bool CTA2>
+__device__ __forceinline__ void tile_rows(int m_blk, int& row0, int& row1) {
+  const int first = CTA2 ? (m_blk & ~1) : m_blk;
+  row0 = first * BLOCK_M;
+  row1 = row0 + (CTA2 ? 2 : 1) * BLOCK_M;
+}
+template <bool CTA2>
+__device__ __forceinline__ bool tile_skipped(const GemmParams& p, int m_blk, int n0) {
+  if (p.tri != 1) return false;
+  int r0, r1;
+  tile_rows<CTA2>(m_blk, r0, r1);
+  return n0 >= r1;
+}
+template <bool CTA2>
+__device__ __forceinline__ void tile_k_range(const GemmParams& p, int m_blk, int& kb0, int& kb1) {
+  kb0 = 0;
+  kb1 = p.num_k;
+  if (p.tri < 2) return;
+  int r0, r1;
+  tile_rows<CTA2>(m_blk, r0, r1);
+  if (p.tri == 2) kb1 = min(p.num_k, (r1 + BLOCK_K - 1) / BLOCK_K);
+  else kb0 = min(p.num_k - 1, r0 / BLOCK_K);
+}
 
 // CTA2: the tile is computed by a CTA pair (cta_group::2): 256 x BN output, each CTA holds its 128 rows of A and
 // half of the B rows per stage, so a stage is 32 KB instead of 48 KB and six stages fit.
@@ -280,6 +310,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         m_blk = CTA2 ? m_blk * 2 + cta_rank : permute_m_block(m_blk, p);
         const int m0 = m_blk * BLOCK_M, n0 = n_blk * BN;
         const int nb0 = n0 + cta_rank * C::B_ROWS;  // this CTA's share of the B rows (all of them without pairing)
+        if (tile_skipped<CTA2>(p, m_blk, n0)) continue;
+        int kb0, kb1;
+        tile_k_range<CTA2>(p, m_blk, kb0, kb1);
         if (p.comm.mode == COMM_AG && m0 / p.comm.rows_per_rank != p.comm.rank) {
           // rows of a remote shard: wait until a copy CTA has landed this 128-row block, then make the
           // generic-proxy writes visible to the TMA (async proxy) reads that follow
@@ -292,7 +325,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           spin_until_ge(&p.comm.blk_flags[n_blk], (uint32_t)((hi - n0) / COPY_ROWS), false);
           asm volatile("fence.proxy.async;" ::: "memory");
         }
-        for (int kb = 0; kb < p.num_k; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
           uint8_t* sb = sa + C::A_BYTES;
@@ -340,10 +373,18 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int t = tile0; t < total_tiles; t += tstride) {
+        int kb0 = 0, kb1 = p.num_k;
+        if (p.tri != 0) {
+          int b, m_blk, n_blk;
+          tile_coords(t, p, num_m_eff, b, m_blk, n_blk);
+          m_blk = CTA2 ? m_blk * 2 : m_blk;
+          if (tile_skipped<CTA2>(p, m_blk, n_blk * BN)) continue;
+          tile_k_range<CTA2>(p, m_blk, kb0, kb1);
+        }
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
-        for (int kb = 0; kb < p.num_k; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
@@ -352,8 +393,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           const uint64_t db = make_smem_desc(sb, hi_b);
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            if (CTA2) umma_f16_2sm(tmem_d, da + uint64_t(k * adv_a), db + uint64_t(k * adv_b), p.idesc, (kb | k) != 0);
-            else umma_f16(tmem_d, da + uint64_t(k * adv_a), db + uint64_t(k * adv_b), p.idesc, (kb | k) != 0);
+            if (CTA2) umma_f16_2sm(tmem_d, da + uint64_t(k * adv_a), db + uint64_t(k * adv_b), p.idesc, (kb != kb0) || k != 0);
+            else umma_f16(tmem_d, da + uint64_t(k * adv_a), db + uint64_t(k * adv_b), p.idesc, (kb != kb0) || k != 0);
           }
           // frees the smem slot (in both CTAs of a pair) once these MMAs retire
           if (CTA2) umma_commit_2sm(&empty_bar[stage]);
@@ -476,6 +517,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       m_blk = CTA2 ? m_blk * 2 + cta_rank : permute_m_block(m_blk, p);
       const int row = m_blk * BLOCK_M + ew * 32 + lane;
       const int n0 = n_blk * BN;
+      if (tile_skipped<CTA2>(p, m_blk, n0)) continue;
       // reduce-scatter: this tile's rows belong to rank `dest`; write into its staging slot for this rank
       int dest = 0;
       char* c_base = reinterpret_cast<char*>(p.C);
@@ -807,7 +849,12 @@ static int gemm_impl(void* stream, int in_dtype, int out_dtype, int M, int N, in
   SMPK_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && (a_bs % 8) == 0 && (b_bs % 8) == 0,
                "smpk_gemm: TMA needs 16-byte aligned strides (lda=%d ldb=%d a_bs=%lld b_bs=%lld)", lda, ldb, a_bs, b_bs);
   SMPK_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "smpk_gemm: operand pointers must be 16-byte aligned");
+  const int tri = (epi >> 8) & 3;       // causal structure rides in bits 8-9 of the epilogue argument
+  epi &= 0xff;
   SMPK_REQUIRE(epi >= 0 && epi <= 4, "smpk_gemm: bad epilogue mode %d", epi);
+  SMPK_REQUIRE(tri == 0 || (comm == nullptr && (tri == 1 ? M == N : M == K) && (tri != 3 || a_mn_major)),
+               "smpk_gemm: causal structure %d needs a square problem (M=%d N=%d K=%d) and no fused collective", tri, M,
+               N, K);
   SMPK_REQUIRE(!(epi >= 3) || R != nullptr, "smpk_gemm: dGELU epilogue needs the pre-activation in R");
 
   GemmParams p;
@@ -821,7 +868,7 @@ static int gemm_impl(void* stream, int in_dtype, int out_dtype, int M, int N, in
   p.aux = aux;
   p.R = R; p.ldr = ldr; p.r_bs = r_bs; p.r_dtype = r_dtype;
   p.bias = bias; p.bias_dtype = bias_dtype;
-  p.alpha = alpha; p.beta = beta; p.epi = epi;
+  p.alpha = alpha; p.beta = beta; p.epi = epi; p.tri = tri;
   p.idesc = (in_dtype == SMPK_BF16) ? 1u : 0u;  // format code, expanded in launch<>
   if (comm != nullptr) {
     CommParams& c = p.comm;

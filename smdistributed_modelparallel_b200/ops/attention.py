@@ -184,6 +184,54 @@ def tokens_to_heads(x, heads):
     return _HeadTranspose.apply(x.reshape(B, S, heads, hd // heads), True)
 
 
+class _CausalAttention(torch.autograd.Function):
+    """softmax(scale q k^T + causal mask) v with every GEMM told about the triangle: score tiles above the
+    diagonal are never computed or written, and the products with P / dS (lower triangular) only reduce over the
+    non-zero part - about 44 % of the attention FLOPs and score traffic at S = 2048."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, scale):
+        from .gemm import gemm
+
+        BH, S, d = q.shape
+        scores = torch.empty(BH, S, S, dtype=q.dtype, device=q.device)
+        gemm(q, k, out=scores, causal="lower_out")
+        probs = torch.empty_like(scores)
+        N.count_launch()
+        N.call("smpk_softmax_fwd", N.stream_ptr(q.device), scores.data_ptr(), probs.data_ptr(), N.dtype_code(q.dtype),
+               None, 1, float(scale), BH, 1, S, S)
+        del scores
+        out = gemm(probs, v, b_mn_major=True, causal="lower_a")
+        ctx.save_for_backward(q, k, v, probs)
+        ctx.scale = scale
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        from .gemm import gemm
+
+        q, k, v, probs = ctx.saved_tensors
+        dout = dout.contiguous()
+        BH, S, d = q.shape
+        dv = gemm(probs, dout, a_mn_major=True, b_mn_major=True, causal="lower_at")      # P^T dO
+        dp = torch.empty_like(probs)
+        gemm(dout, v, out=dp, causal="lower_out")                                        # dO V^T (lower tiles)
+        ds = torch.empty_like(probs)
+        N.count_launch()
+        N.call("smpk_softmax_bwd", N.stream_ptr(q.device), dp.data_ptr(), probs.data_ptr(), ds.data_ptr(),
+               N.dtype_code(q.dtype), 1, float(ctx.scale), BH, S, S)
+        del dp
+        dq = gemm(ds, k, b_mn_major=True, causal="lower_a")                              # dS K
+        dk = gemm(ds, q, a_mn_major=True, b_mn_major=True, causal="lower_at")            # dS^T Q
+        return dq, dk, dv, None
+
+
+def _causal_fast_path(q, k, mask, window, dropout_p, training) -> bool:
+    return (q.is_cuda and mask is None and window is None and q.shape[2] == k.shape[2] and q.shape[2] % 8 == 0 and q.shape[2] <= 8192
+            and q.shape[3] % 8 == 0 and q.dtype in (torch.bfloat16, torch.float16) and not (dropout_p > 0.0 and training)
+            and N.available())
+
+
 # --------------------------------------------------------------------------------- core attention
 def core_attention(q, k, v, *, causal: bool = True, mask=None, scale: float | None = None, dropout_p: float = 0.0,
                    training: bool = True, window: int | None = None):
@@ -195,6 +243,10 @@ def core_attention(q, k, v, *, causal: bool = True, mask=None, scale: float | No
     B, h, Sq, d = q.shape
     Sk = k.shape[2]
     scale = (1.0 / math.sqrt(d)) if scale is None else scale
+    if causal and _causal_fast_path(q, k, mask, window, dropout_p, training):
+        ctx = _CausalAttention.apply(q.reshape(B * h, Sq, d).contiguous(), k.reshape(B * h, Sk, d).contiguous(),
+                                     v.reshape(B * h, Sk, d).contiguous(), float(scale))
+        return ctx.reshape(B, h, Sq, d)
     scores = bmm_nt(q.reshape(B * h, Sq, d), k.reshape(B * h, Sk, d))
     if window is not None:
         i = torch.arange(Sq, device=q.device)[:, None] + (Sk - Sq)

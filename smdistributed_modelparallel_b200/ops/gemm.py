@@ -21,6 +21,8 @@ EPI_NONE, EPI_GELU_TANH, EPI_GELU_ERF, EPI_DGELU_TANH, EPI_DGELU_ERF = range(5)
 _EPI_BY_NAME = {"none": EPI_NONE, "gelu_tanh": EPI_GELU_TANH, "gelu_erf": EPI_GELU_ERF,
                 "dgelu_tanh": EPI_DGELU_TANH, "dgelu_erf": EPI_DGELU_ERF}
 
+_TRI = {None: 0, "lower_out": 1, "lower_a": 2, "lower_at": 3}
+
 # diagnostics: how many GEMMs ran natively / fell back to torch.matmul (shape or alignment limits)
 stats = {"native": 0, "fallback": 0}
 
@@ -92,15 +94,21 @@ def _native_ok(a, b, out, residual, bias):
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
          out: torch.Tensor | None = None, out_dtype: torch.dtype | None = None, bias: torch.Tensor | None = None,
          residual: torch.Tensor | None = None, alpha: float = 1.0, beta: float = 1.0, epilogue: str | int = "none",
-         aux_out: torch.Tensor | None = None) -> torch.Tensor:
+         aux_out: torch.Tensor | None = None, causal: str | None = None) -> torch.Tensor:
     """``out = epilogue(alpha * A @ B^T)`` with A logical [M,K] and B logical [N,K] (optionally batched).
 
     ``a`` is stored ``[..., M, K]`` (K-major) or, with ``a_mn_major``, ``[..., K, M]``; likewise ``b``
     is ``[..., N, K]`` or ``[..., K, N]``.  2-D or 3-D (leading batch) tensors; the last dimension
     must be contiguous.  ``residual`` is added scaled by ``beta`` (it may be ``out`` itself for in-place
     accumulation) or, for the ``dgelu_*`` epilogues, is the saved pre-activation.
+
+    ``causal`` declares triangular structure of a square attention problem so the kernel skips the work the
+    causal mask makes irrelevant: ``"lower_out"`` - only output tiles touching the lower triangle are computed
+    (the rest of ``out`` is left untouched); ``"lower_a"`` - logical A [M, K] is lower triangular;
+    ``"lower_at"`` - A is given MN-major and its transpose... i.e. stored [K, M] lower triangular.
     """
     epi = _EPI_BY_NAME[epilogue] if isinstance(epilogue, str) else int(epilogue)
+    tri = _TRI[causal]
     assert a.dim() == b.dim() and a.dim() in (2, 3), "gemm expects 2-D or batched 3-D operands"
     batch = a.shape[0] if a.dim() == 3 else 1
     if a_mn_major:
@@ -162,7 +170,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
         N.ptr(residual), residual.stride(-2) if residual is not None else 0,
         bs(residual) if residual is not None else 0,
         N.dtype_code(residual.dtype) if residual is not None else 0,
-        N.ptr(aux_out), float(alpha), float(beta), epi, _max_ctas,
+        N.ptr(aux_out), float(alpha), float(beta), epi | (tri << 8), _max_ctas,
     )
     return out
 
