@@ -14,7 +14,9 @@ namespace {
 
 constexpr float NEG_BIG = -1e30f;
 
-// mode 0: no mask, 1: causal (col <= row + Sk - Sq), 2: byte mask [B,1,Sq,Sk] (non-zero = masked out)
+// mode 0: no mask, 1: causal (col <= row + Sk - Sq), 2: byte mask [B,1,Sq,Sk] (non-zero = masked out),
+// 3: causal, and only columns below the next multiple of 256 past the diagonal are written (the triangle-aware
+//    GEMMs that consume the result never read further; saves the zero fill of the upper triangle)
 template <int NV>
 __global__ void softmax_fwd_kernel(const void* __restrict__ x, void* __restrict__ y, int dtype,
                                    const uint8_t* __restrict__ mask, int mode, float scale, int heads, int Sq, int Sk,
@@ -24,7 +26,8 @@ __global__ void softmax_fwd_kernel(const void* __restrict__ x, void* __restrict_
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
     const int q = (int)(row % Sq);
     const long long bh = row / Sq;
-    const int limit = (mode == 1) ? min(Sk, q + 1 + (Sk - Sq)) : Sk;  // columns [0, limit) are visible
+    const int limit = (mode == 1 || mode == 3) ? min(Sk, q + 1 + (Sk - Sq)) : Sk;  // columns [0, limit) are visible
+    const int wlimit = (mode == 3) ? min(Sk, (limit + 255) & ~255) : Sk;            // columns [0, wlimit) are written
     const uint8_t* mrow = (mode == 2) ? mask + ((bh / heads) * (long long)Sq + q) * Sk : nullptr;
     const size_t base = (size_t)row * Sk;
     float v[NV][8];
@@ -61,7 +64,7 @@ __global__ void softmax_fwd_kernel(const void* __restrict__ x, void* __restrict_
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int vi = threadIdx.x + i * blockDim.x;
-      if (vi < nvec) {
+      if (vi < nvec && vi * 8 < wlimit) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[i][j] *= inv;
         store8(y, dtype, base + (size_t)vi * 8, v[i]);
@@ -77,7 +80,7 @@ __global__ void softmax_fwd_scalar_kernel(const void* __restrict__ x, void* __re
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
     const int q = (int)(row % Sq);
     const long long bh = row / Sq;
-    const int limit = (mode == 1) ? min(Sk, q + 1 + (Sk - Sq)) : Sk;
+    const int limit = (mode == 1 || mode == 3) ? min(Sk, q + 1 + (Sk - Sq)) : Sk;   // scalar path: mode 3 fills whole rows
     const uint8_t* mrow = (mode == 2) ? mask + ((bh / heads) * (long long)Sq + q) * Sk : nullptr;
     const size_t base = (size_t)row * Sk;
     float mx = NEG_BIG;
@@ -105,6 +108,7 @@ __global__ void softmax_bwd_kernel(const void* __restrict__ dy, const void* __re
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
     const int q = (int)(row % Sq);
     const int limit = causal ? min(Sk, q + 1 + (Sk - Sq)) : Sk;
+    const int wlimit = (causal == 2) ? min(Sk, (limit + 255) & ~255) : Sk;
     const size_t base = (size_t)row * Sk;
     float yv[NV][8], dv[NV][8];
     float dot = 0.f;
@@ -128,7 +132,7 @@ __global__ void softmax_bwd_kernel(const void* __restrict__ dy, const void* __re
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int vi = threadIdx.x + i * blockDim.x;
-      if (vi < nvec) {
+      if (vi < nvec && vi * 8 < wlimit) {
         float o[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = scale * yv[i][j] * (dv[i][j] - dot);
@@ -163,7 +167,7 @@ inline void pick_geometry(int Sk, int& threads, int& nv) {
 // x, y: [batch*heads, Sq, Sk] contiguous; mask (mode 2): uint8 [batch, 1, Sq, Sk].
 SMPK_API int smpk_softmax_fwd(void* stream, const void* x, void* y, int dtype, const void* mask, int mode, float scale,
                               int batch_heads, int heads, int Sq, int Sk) {
-  SMPK_REQUIRE(mode >= 0 && mode <= 2, "softmax_fwd: bad mode %d", mode);
+  SMPK_REQUIRE(mode >= 0 && mode <= 3, "softmax_fwd: bad mode %d", mode);
   SMPK_REQUIRE(mode != 2 || (mask != nullptr && heads > 0), "softmax_fwd: mask mode needs mask and heads");
   const long long rows = (long long)batch_heads * Sq;
   if (rows == 0 || Sk == 0) return 0;

@@ -199,7 +199,7 @@ class _CausalAttention(torch.autograd.Function):
         probs = torch.empty_like(scores)
         N.count_launch()
         N.call("smpk_softmax_fwd", N.stream_ptr(q.device), scores.data_ptr(), probs.data_ptr(), N.dtype_code(q.dtype),
-               None, 1, float(scale), BH, 1, S, S)
+               None, 3, float(scale), BH, 1, S, S)       # mode 3: causal, zero fill only up to the next 256 columns
         del scores
         out = gemm(probs, v, b_mn_major=True, causal="lower_a")
         ctx.save_for_backward(q, k, v, probs)
@@ -219,7 +219,7 @@ class _CausalAttention(torch.autograd.Function):
         ds = torch.empty_like(probs)
         N.count_launch()
         N.call("smpk_softmax_bwd", N.stream_ptr(q.device), dp.data_ptr(), probs.data_ptr(), ds.data_ptr(),
-               N.dtype_code(q.dtype), 1, float(ctx.scale), BH, S, S)
+               N.dtype_code(q.dtype), 2, float(ctx.scale), BH, S, S)
         del dp
         dq = gemm(ds, k, b_mn_major=True, causal="lower_a")                              # dS K
         dk = gemm(ds, q, a_mn_major=True, b_mn_major=True, causal="lower_at")            # dS^T Q
