@@ -174,10 +174,10 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t v, boo
 
 // Order m-blocks so communication overlaps compute: AG starts with the local shard and walks the ring;
 // RS finishes with the local shard (remote tiles leave first).
-__device__ __forceinline__ int permute_m_block(int m_blk, const GemmParams& p) {
+__device__ __forceinline__ int permute_m_block(int m_blk, const GemmParams& p, int blocks_per_tile = 1) {
   const CommParams& c = p.comm;
   if (c.mode != COMM_AG && c.mode != COMM_RS) return m_blk;
-  const int mpr = c.rows_per_rank / BLOCK_M;
+  const int mpr = c.rows_per_rank / (BLOCK_M * blocks_per_tile);   // tiles (single blocks or CTA-pair tiles) per rank
   const int ci = m_blk / mpr, within = m_blk - ci * mpr;
   const int chunk = (c.mode == COMM_AG) ? (c.rank + ci) % c.nranks : (c.rank + 1 + ci) % c.nranks;
   return chunk * mpr + within;
@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       for (int t = tile0; t < total_tiles; t += tstride) {
         int b, m_blk, n_blk;
         tile_coords(t, p, num_m_eff, b, m_blk, n_blk);
-        m_blk = CTA2 ? m_blk * 2 + cta_rank : permute_m_block(m_blk, p);
+        m_blk = CTA2 ? permute_m_block(m_blk, p, 2) * 2 + cta_rank : permute_m_block(m_blk, p);
         const int m0 = m_blk * BLOCK_M, n0 = n_blk * BN;
         const int nb0 = n0 + cta_rank * C::B_ROWS;  // this CTA's share of the B rows (all of them without pairing)
         if (tile_skipped<CTA2>(p, m_blk, n0)) continue;
@@ -514,7 +514,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     for (int t = tile0; t < total_tiles; t += tstride) {
       int b, m_blk, n_blk;
       tile_coords(t, p, num_m_eff, b, m_blk, n_blk);
-      m_blk = CTA2 ? m_blk * 2 + cta_rank : permute_m_block(m_blk, p);
+      m_blk = CTA2 ? permute_m_block(m_blk, p, 2) * 2 + cta_rank : permute_m_block(m_blk, p);
       const int row = m_blk * BLOCK_M + ew * 32 + lane;
       const int n0 = n_blk * BN;
       if (tile_skipped<CTA2>(p, m_blk, n0)) continue;
@@ -729,9 +729,19 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStre
   const int total = p.batch * num_m_eff * p.num_n;
   int grid = smpk::num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (CTA2) grid &= ~1;                          // whole pairs
+  const int per_tile = CTA2 ? 2 : 1;
+  if (p.comm.mode != COMM_AGB && per_tile * total < grid) grid = per_tile * total;
+  // (gathered-weight mode: the copy warps of EVERY resident CTA gather the unit, so the grid stays full)
+  if (p.comm.mode == COMM_AG) {
+    // arrival counters of the row blocks start at zero for this launch
+    SMPK_CHECK_CUDA(cudaMemsetAsync(p.comm.blk_flags, 0, sizeof(uint32_t) * (size_t)p.num_m, stream));
+  }
+  if (p.comm.mode == COMM_AGB) {
+    const size_t nblk = (size_t)((p.comm.total_rows + BN - 1) / BN);
+    SMPK_CHECK_CUDA(cudaMemsetAsync(p.comm.blk_flags, 0, sizeof(uint32_t) * nblk, stream));
+  }
   if (CTA2) {
-    grid &= ~1;                                  // whole pairs
-    if (2 * total < grid) grid = 2 * total;
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3((unsigned)grid);
@@ -747,18 +757,6 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams& p, cudaStre
     cfg.numAttrs = 1;
     SMPK_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, CTA2>, ta, tb, p));
     return 0;
-  }
-  if (total < grid) grid = total;
-  if (p.comm.mode == COMM_AG) {
-    // arrival counters of the row blocks start at zero for this launch
-    SMPK_CHECK_CUDA(cudaMemsetAsync(p.comm.blk_flags, 0, sizeof(uint32_t) * (size_t)p.num_m, stream));
-  }
-  if (p.comm.mode == COMM_AGB) {
-    // the copy warps of EVERY resident CTA gather the unit, so the grid is never cut below the SM count
-    grid = smpk::num_sms();
-    if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
-    const size_t nblk = (size_t)((p.comm.total_rows + BN - 1) / BN);
-    SMPK_CHECK_CUDA(cudaMemsetAsync(p.comm.blk_flags, 0, sizeof(uint32_t) * nblk, stream));
   }
   gemm_tcgen05_kernel<BN, CTA2><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
   SMPK_CHECK_CUDA(cudaGetLastError());
@@ -889,7 +887,9 @@ static int gemm_impl(void* stream, int in_dtype, int out_dtype, int M, int N, in
   // problems stay on single CTAs
   const long long pair_tiles = (long long)batch * ((p.num_m + 1) / 2) * ((N + 255) / 256);
   const int pm = pair_mode();
-  const bool pair = BN == 256 && comm == nullptr && M > BLOCK_M && pm > 0 && (pm == 2 || pair_tiles >= smpk::num_sms() / 4);
+  // (token all-gather / reduce-scatter modes order tiles by owning rank, so a pair tile must not straddle two ranks)
+  const bool comm_ok = comm == nullptr || comm->mode == COMM_AGB || comm->rows_per_rank % (2 * BLOCK_M) == 0;
+  const bool pair = BN == 256 && comm_ok && M > BLOCK_M && pm > 0 && (pm == 2 || pair_tiles >= smpk::num_sms() / 4);
   CUtensorMap ta, tb;
   int rc = make_operand_map(&ta, in_dtype, A, M, K, batch, lda, a_bs, p.a_mn_major, BLOCK_M);
   if (rc) return rc;
