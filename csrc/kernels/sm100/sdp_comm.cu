@@ -124,16 +124,38 @@ __global__ void __launch_bounds__(256) sdp_reduce_kernel(ReduceArgs a) {
       goff[u] = (q * a.nranks + a.rank) * pvec + (i - q * pvec);
       acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    // fixed rank order: the sum is bitwise identical on every run
+    // optimizer state of this trip, requested before the (slower) peer reads so it is there when they return
+    float4 pre_p[RU], pre_m[RU], pre_s[RU];
+    if (a.mode == 1) {
 #pragma unroll
-    for (int j = 0; j < MAX_RANKS; ++j) {
+      for (int u = 0; u < RU; ++u) {
+        const long long i = idx[u] < nvec ? idx[u] : 0;
+        pre_p[u] = reinterpret_cast<const float4*>(a.master)[i];
+        pre_m[u] = reinterpret_cast<const float4*>(a.exp_avg)[i];
+        pre_s[u] = reinterpret_cast<const float4*>(a.exp_avg_sq)[i];
+      }
+    }
+    // fixed rank order: the sum is bitwise identical on every run.  Ranks are read two at a time so that the
+    // loads of both (2 x RU x 16 B per thread) are in flight before either is consumed.
+#pragma unroll
+    for (int j = 0; j < MAX_RANKS; j += 2) {
       if (j < a.nranks) {
-        float4 v[RU];
-        const float4* src = reinterpret_cast<const float4*>(a.peer_grad[j]);
+        const bool two = j + 1 < a.nranks;
+        float4 v0[RU], v1[RU];
+        const float4* s0 = reinterpret_cast<const float4*>(a.peer_grad[j]);
+        const float4* s1 = reinterpret_cast<const float4*>(a.peer_grad[two ? j + 1 : j]);
 #pragma unroll
-        for (int u = 0; u < RU; ++u) v[u] = ld_nc_f4(src + goff[u]);
+        for (int u = 0; u < RU; ++u) v0[u] = ld_nc_f4(s0 + goff[u]);
+        if (two) {
 #pragma unroll
-        for (int u = 0; u < RU; ++u) { acc[u].x += v[u].x; acc[u].y += v[u].y; acc[u].z += v[u].z; acc[u].w += v[u].w; }
+          for (int u = 0; u < RU; ++u) v1[u] = ld_nc_f4(s1 + goff[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < RU; ++u) { acc[u].x += v0[u].x; acc[u].y += v0[u].y; acc[u].z += v0[u].z; acc[u].w += v0[u].w; }
+        if (two) {
+#pragma unroll
+          for (int u = 0; u < RU; ++u) { acc[u].x += v1[u].x; acc[u].y += v1[u].y; acc[u].z += v1[u].z; acc[u].w += v1[u].w; }
+        }
       }
     }
 #pragma unroll
@@ -151,9 +173,7 @@ __global__ void __launch_bounds__(256) sdp_reduce_kernel(ReduceArgs a) {
         reinterpret_cast<float4*>(a.grad_shard)[i] = make_float4(g[0], g[1], g[2], g[3]);
         continue;
       }
-      float4 p4 = reinterpret_cast<const float4*>(a.master)[i];
-      float4 m4 = reinterpret_cast<const float4*>(a.exp_avg)[i];
-      float4 s4 = reinterpret_cast<const float4*>(a.exp_avg_sq)[i];
+      const float4 p4 = pre_p[u], m4 = pre_m[u], s4 = pre_s[u];
       float p[4] = {p4.x, p4.y, p4.z, p4.w}, m[4] = {m4.x, m4.y, m4.z, m4.w}, sq[4] = {s4.x, s4.y, s4.z, s4.w};
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
