@@ -129,3 +129,43 @@ def test_module_manager_names_partitions_and_marks():
     assert mm.is_marked_for_tp(net.a) and mm.get_tp_config(net.a) == {"foo": 1}
     with pytest.raises(Exception):
         mm.set_partition(net.a, 5)
+
+
+def test_leader_scheduler_order_is_static():
+    """The leader's task order depends only on (microbatches, window, warm): tasks are suspendable threads, the
+    scheduler starts ``warm`` of them, then alternates resume-oldest / start-next inside the window - regardless
+    of when results arrive (here they are all available at once)."""
+    from smdistributed_modelparallel_b200.runtime import server as S
+
+    class FakeServer:
+        def __init__(self):
+            self.stash, self.log = {}, []
+            import torch
+            self.state = type("St", (), {"device": torch.device("cpu")})()
+
+        def _pump_one(self, timeout_ms):
+            raise AssertionError("every awaited key is already stashed in this test")
+
+        def _run_microbatch(self, mb, phase):
+            for seg in range(3):                       # forward chunk, head + backward request, backward chunk
+                self.log.append((mb, seg))
+                if seg < 2:
+                    key = ("K", mb, seg)
+                    self.stash[key] = True
+                    S._task_local.task.suspend(key)
+                    self.stash.pop(key)
+
+    def order(nmb, window, warm):
+        srv = FakeServer()
+        S._Scheduler(srv, [(mb, "both") for mb in range(nmb)], window, warm=warm).run()
+        return srv.log
+
+    got = order(4, 4, 2)
+    assert got == [(0, 0), (1, 0), (0, 1), (2, 0), (1, 1), (3, 0), (0, 2), (2, 1), (1, 2), (3, 1), (2, 2), (3, 2)], got
+    assert order(4, 4, 2) == got                                    # repeatable
+    fill = order(3, 3, 3)                                           # warm == window: fill first, then oldest-first
+    assert fill[:3] == [(0, 0), (1, 0), (2, 0)] and fill[3] == (0, 1)
+    one = order(3, 1, 1)                                            # window 1: strictly one microbatch at a time
+    assert one == [(mb, seg) for mb in range(3) for seg in range(3)]
+    every = sorted(order(8, 4, 2))
+    assert every == [(mb, seg) for mb in range(8) for seg in range(3)]
