@@ -369,10 +369,13 @@ class DistributedTransformerOutputLayer(DistributedModule):
         if h.dtype != self.dense1_weight.dtype:
             h = h.to(self.dense1_weight.dtype)
         mode = _gelu_mode(self.activation)
-        inter = tp_ops.ag_linear(h, self.dense1_weight, self.dense1_bias, mode, g)
-        if mode is None:
-            inter = self._act_other(inter)
-        out = tp_ops.linear_rs(inter, self.dense2_weight, self.dense2_bias, g)
+        if mode is not None and tp_ops.fused_mlp_applicable(h, self.dense1_weight, g):
+            out = tp_ops.FusedMLP.apply(h, self.dense1_weight, self.dense1_bias, self.dense2_weight, self.dense2_bias, mode)
+        else:
+            inter = tp_ops.ag_linear(h, self.dense1_weight, self.dense1_bias, mode, g)
+            if mode is None:
+                inter = self._act_other(inter)
+            out = tp_ops.linear_rs(inter, self.dense2_weight, self.dense2_bias, g)
         out = F.dropout(out, self.hidden_dropout_prob, self.training)
         out = out.to(x2.dtype) + x2
         if self.layernorm is not None:
@@ -445,6 +448,21 @@ class DistributedTransformerLayer(DistributedModule):
         mask = _full_mask(attention_mask, b * t, g)
         mode = _gelu_mode(out.activation)
         shared_ln = out.pre_layernorm_mod is None
+        if mode is not None and tp_ops.fused_mlp_applicable(ha, out.dense1_weight, g):
+            # one rank: QKV first (sharded data parallelism gathers the unit inside that GEMM), then the whole MLP
+            # as one fused function with the attention branch added by its last GEMM's epilogue
+            qkv = tp_ops.ag_linear(ha, att.qkv_weight, att.qkv_bias, None, g)
+            if shared_ln:
+                hm = ha
+            else:
+                hm = out.pre_layernorm_mod(x2)
+                hm = hm.to(wdtype) if hm.dtype != wdtype else hm
+            ctx2 = att.attention_core(qkv, b * t, S, mask)
+            p1 = tp_ops.RowParallelLinear.apply(ctx2, att.dense_weight, att.dense_bias, g, False)
+            y = tp_ops.FusedMLP.apply(hm, out.dense1_weight, out.dense1_bias, out.dense2_weight, out.dense2_bias, mode, p1)
+            y = F.dropout(y, self.hidden_dropout_prob, self.training)
+            y = y.to(x2.dtype) + x2
+            return y.reshape(b, S, H)
         if shared_ln:
             qkv, xg = tp_ops.ag_linear(ha, att.qkv_weight, att.qkv_bias, None, g, want_gathered=True)
             inter = tp_ops.ColumnParallelLinear.apply(xg, out.dense1_weight, out.dense1_bias, mode, g, True)

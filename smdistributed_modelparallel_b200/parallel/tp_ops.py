@@ -179,6 +179,40 @@ class RowParallelLinear(torch.autograd.Function):
         return dx, dw, db, None, None
 
 
+class FusedMLP(torch.autograd.Function):
+    """y = gelu(x W1^T + b1) W2^T + b2 on one rank (tensor-parallel degree 1), four GEMM launches forward + backward
+    plus wgrads: GELU rides the first GEMM's epilogue, an optional ``residual`` [T, H] is added by the second GEMM's
+    epilogue, and in backward GELU' rides the epilogue of the dgrad GEMM through W2 (``(dy W2) * gelu'(pre)``), so no elementwise pass over the [T, 4H] intermediate remains."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, activation, residual=None):
+        ctx.activation = activation
+        ctx.has_residual = residual is not None
+        inter = torch.empty(x.shape[0], w1.shape[0], dtype=x.dtype, device=x.device)
+        need = any(ctx.needs_input_grad[:5])
+        pre = torch.empty_like(inter) if need else None
+        gemm(x, w1, bias=b1, out=inter, epilogue=f"gelu_{activation}", aux_out=pre)
+        y = gemm(inter, w2, bias=b2, residual=residual, beta=1.0)      # + residual in the epilogue when given
+        ctx.save_for_backward(x, w1, b1, w2, b2, pre, inter)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w1, b1, w2, b2, pre, inter = ctx.saved_tensors
+        dy = dy if dy.is_contiguous() else dy.contiguous()
+        dz = gemm(dy, w2, b_mn_major=True, residual=pre, epilogue=f"dgelu_{ctx.activation}")   # d(pre-activation)
+        dw2 = _wgrad(dy, inter, w2) if ctx.needs_input_grad[3] else None
+        db2 = _bgrad(dy, b2) if (b2 is not None and ctx.needs_input_grad[4]) else None
+        dx = gemm(dz, w1, b_mn_major=True) if ctx.needs_input_grad[0] else None
+        dw1 = _wgrad(dz, x, w1) if ctx.needs_input_grad[1] else None
+        db1 = _bgrad(dz, b1) if (b1 is not None and ctx.needs_input_grad[2]) else None
+        return dx, dw1, db1, dw2, db2, None, (dy if ctx.has_residual else None)
+
+
+def fused_mlp_applicable(x, w1, group) -> bool:
+    return _group_size(group) == 1 and x.is_cuda and x.dtype in (torch.bfloat16, torch.float16) and w1.dtype == x.dtype
+
+
 def _ag(x, group):
     if _group_size(group) == 1:
         return x

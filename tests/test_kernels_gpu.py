@@ -327,6 +327,38 @@ def test_causal_attention_triangular_gemms(B, h, S, d):
     _report("causal attention dv", dv, rv, 3e-2)
 
 
+@pytest.mark.parametrize("act", ["tanh", "erf"])
+def test_fused_mlp(act):
+    """gelu(x W1^T + b1) W2^T + b2 + residual as one autograd function (GELU and GELU' in GEMM epilogues) against
+    fp32 PyTorch: output and every gradient, with fp32 main_grad accumulation for the weights."""
+    from smdistributed_modelparallel_b200.parallel.tp_ops import FusedMLP
+
+    torch.manual_seed(21)
+    T, H, I = 512, 256, 1024
+    bf = torch.bfloat16
+    x = (torch.randn(T, H, device=DEV, dtype=bf) * 0.5).requires_grad_(True)
+    res = (torch.randn(T, H, device=DEV, dtype=bf) * 0.5).requires_grad_(True)
+    w1 = (torch.randn(I, H, device=DEV, dtype=bf) * 0.05).requires_grad_(True)
+    b1 = (torch.randn(I, device=DEV, dtype=bf) * 0.1).requires_grad_(True)
+    w2 = (torch.randn(H, I, device=DEV, dtype=bf) * 0.05).requires_grad_(True)
+    b2 = (torch.randn(H, device=DEV, dtype=bf) * 0.1).requires_grad_(True)
+    w1.main_grad = torch.zeros(I, H, device=DEV)              # the reducer's fp32 buffer: wgrad accumulates into it
+    y = FusedMLP.apply(x, w1, b1, w2, b2, act, res)
+    gy = torch.randn_like(y)
+    dx, dres, db1, dw2, db2 = torch.autograd.grad(y, (x, res, b1, w2, b2), gy, allow_unused=True)
+    f = [t.detach().float().requires_grad_(True) for t in (x, res, w1, b1, w2, b2)]
+    h = F.gelu(f[0] @ f[2].t() + f[3], approximate="tanh" if act == "tanh" else "none")
+    yr = h @ f[4].t() + f[5] + f[1]
+    g = torch.autograd.grad(yr, f, gy.float())
+    _report("fused mlp y", y, yr, 2e-2)
+    _report("fused mlp dx", dx, g[0], 3e-2)
+    _report("fused mlp dres", dres, g[1], 1e-6)
+    _report("fused mlp dw1 (main_grad)", w1.main_grad, g[2], 3e-2)
+    _report("fused mlp db1", db1, g[3], 3e-2)
+    _report("fused mlp dw2", dw2, g[4], 3e-2)
+    _report("fused mlp db2", db2, g[5], 3e-2)
+
+
 def test_multi_tensor_ops():
     from smdistributed_modelparallel_b200.ops import multi_tensor as MT
 
