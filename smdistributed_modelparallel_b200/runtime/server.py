@@ -233,12 +233,83 @@ class ExecutionServer:
         self._orig_forward = {}
 
     # ================================================================== partitioning (first step)
-    def _partition(self):
+    def _trace(self, step_fn, args, kwargs, num_mb):
+        """First-step tracing on the leader (reference torch/patches/tracing.py:41-86, worker.py:248-278): run
+        the step function once on the first microbatch without gradients, wherever the unpartitioned model
+        lives, recording per module the execution order, wall time and bytes of tensors produced.  The
+        partitioner weighs ``memory_weight * memory + (1 - memory_weight) * time`` with these.  Skipped when
+        tracing is off, nothing was requested, or the parameters are not materialised yet (delayed init)."""
+        import time as _time
+
+        st = self.state
+        model = self.model
+        want_t, want_m = model.trace_execution_times, model.trace_memory_usage
+        if st.cfg.skip_tracing or not (want_t or want_m) or not self.is_leader:
+            return None, None
+        root = model.module
+        if any(p.is_meta or getattr(p, "_smp_delayed", False) for p in root.parameters()):
+            get_logger().info("tracing skipped: parameters are not materialised (delayed initialisation)")
+            return None, None
+        dev = next((p.device for p in root.parameters()), torch.device("cpu"))
+        mm = st.module_manager
+        trace = mm.trace
+        started = {}
+        hooks = []
+
+        def tensor_bytes(obj):
+            total = [0]
+            map_structure(lambda t: total.__setitem__(0, total[0] + t.numel() * t.element_size())
+                          if torch.is_tensor(t) else None, obj)
+            return total[0]
+
+        def pre(mod, a):
+            name = mm.get_module_name(mod)
+            if name not in trace.order:
+                trace.order.append(name)
+            if dev.type == "cuda":
+                torch.cuda.synchronize(dev)
+            started[mod] = _time.perf_counter()
+            trace.in_bytes[name] = trace.in_bytes.get(name, 0) + tensor_bytes(a)
+
+        def post(mod, a, out):
+            if dev.type == "cuda":
+                torch.cuda.synchronize(dev)
+            name = mm.get_module_name(mod)
+            trace.times[name] = trace.times.get(name, 0.0) + (_time.perf_counter() - started.pop(mod, _time.perf_counter()))
+            nbytes = tensor_bytes(out)
+            trace.out_bytes[name] = trace.out_bytes.get(name, 0) + nbytes
+            trace.memory[name] = trace.memory.get(name, 0) + nbytes
+
+        for m in root.modules():
+            hooks.append(m.register_forward_pre_hook(pre))
+            hooks.append(m.register_forward_hook(post))
+        a, k = step_fn.splitter.preprocess_args(args, kwargs, num_mb, 0)
+        a = map_structure(lambda t: t.to(dev) if torch.is_tensor(t) else t, a)
+        k = map_structure(lambda t: t.to(dev) if torch.is_tensor(t) else t, k)
+        st.is_tracing_flag = True
+        prev_mb = st.microbatch
+        st.microbatch = 0
+        try:
+            with torch.no_grad():
+                step_fn.func(*a, **k)
+        finally:
+            st.is_tracing_flag = False
+            st.microbatch = prev_mb
+            for h in hooks:
+                h.remove()
+        times = {mm.get_module(n): t for n, t in trace.times.items()} if want_t else None
+        memory = {mm.get_module(n): float(b) for n, b in trace.memory.items()} if want_m else None
+        return times, memory
+
+    def _partition(self, step_fn=None, args=None, kwargs=None, num_mb=1):
         from ..pipeline.partition import partition_model
 
         st = self.state
         mm = st.module_manager
-        assignment = partition_model(self.model.module, mm, st.cfg)
+        times = memory = None
+        if step_fn is not None and st.cfg.auto_partition:
+            times, memory = self._trace(step_fn, args, kwargs, num_mb)
+        assignment = partition_model(self.model.module, mm, st.cfg, module_times=times, module_memory=memory)
         # every rank computes the same deterministic assignment; the leader's copy is authoritative
         if self.core.pp_size() > 1:
             if self.is_leader:
@@ -499,12 +570,16 @@ class ExecutionServer:
     def run_model_forward(self, model, args, kwargs):
         root = model.module
         mm = self.state.module_manager
+        if self.state.is_tracing_flag:               # unpartitioned model, executed where it lives
+            return root(*args, **kwargs)
         if mm.get_partition(root) == self.pp_rank:
             return root(*args, **kwargs)
         return self._remote_forward(mm.get_module_name(root), None, self._owner_rank(root), args, kwargs)
 
     def run_model_backward(self, model, tensors, grads):
         """Called from inside the step function: register; the scheduler decides when it runs."""
+        if self.state.is_tracing_flag:
+            return
         mb = self.state.microbatch
         self.deferred_bwd[mb] = (tuple(tensors), tuple(grads))
 
@@ -544,7 +619,7 @@ class ExecutionServer:
     def run_step(self, step_fn, args, kwargs, num_mb):
         st = self.state
         if not self.partitioned:
-            self._partition()
+            self._partition(step_fn, args, kwargs, num_mb)
         self._done_msg = None
         pipe = st.pipeline
         pipe.init_step()

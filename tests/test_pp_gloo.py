@@ -13,7 +13,7 @@ CFG = dict(num_layers=4, num_attention_heads=4, attention_head_size=8, hidden_si
            post_layernorm=False, final_layernorm=True, use_normal_initialization=True)
 
 
-def _worker(rank, world, pipeline, microbatches):
+def _worker(rank, world, pipeline, microbatches, trace=False):
     import copy
 
     import smdistributed_modelparallel_b200 as smp
@@ -22,7 +22,7 @@ def _worker(rank, world, pipeline, microbatches):
     torch.manual_seed(7)
     module = smp.nn.DistributedTransformerLMHead(**CFG)
     oracle = copy.deepcopy(module)
-    model = smp.DistributedModel(module)
+    model = smp.DistributedModel(module, trace_execution_times=trace, trace_memory_usage=trace)
     opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
 
     @smp.step
@@ -48,8 +48,10 @@ def _worker(rank, world, pipeline, microbatches):
         n_local += 1
     part = smp.state.module_manager.partition_info()
     opt.step()
+    tr = smp.state.module_manager.trace
     return {"loss": loss, "oracle": ol.item(), "worst_grad_err": worst, "n_local": n_local,
-            "ranks_used": sorted(set(part.values())), "hops": smp.state.module_manager.hops}
+            "ranks_used": sorted(set(part.values())), "hops": smp.state.module_manager.hops,
+            "traced": len(tr.order), "trace_time": sum(tr.times.values()), "trace_bytes": sum(tr.memory.values())}
 
 
 @pytest.mark.parametrize("pipeline", ["interleaved", "simple"])
@@ -61,6 +63,19 @@ def test_pp2_matches_dense(pipeline):
         assert r["ranks_used"] == [0, 1]
         assert r["n_local"] > 0
     assert sum(r["n_local"] for r in res) > 0
+
+
+def test_pp2_with_first_step_tracing():
+    """trace_execution_times / trace_memory_usage: the leader runs one traced microbatch before partitioning and
+    feeds times and activation sizes to the partitioner; training is unaffected."""
+    res = run_distributed(_worker, 2, "interleaved", 4, True)
+    for r in res:
+        assert abs(r["loss"] - r["oracle"]) < 1e-5, r
+        assert r["worst_grad_err"] < 1e-5, r
+        assert r["ranks_used"] == [0, 1]
+    leader = res[0]
+    assert leader["traced"] > 10 and leader["trace_time"] > 0 and leader["trace_bytes"] > 0, leader
+    assert res[1]["traced"] == 0
 
 
 def _pp_tp_worker(rank, world, window):
