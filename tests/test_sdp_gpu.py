@@ -17,7 +17,7 @@ CFG = dict(num_layers=3, num_attention_heads=4, attention_head_size=32, hidden_s
            post_layernorm=False, final_layernorm=True, use_normal_initialization=True)
 
 
-def _worker(rank, world, fused, clip):
+def _worker(rank, world, fused, clip, ckpt_offload=False):
     import copy
 
     import smdistributed_modelparallel_b200 as smp
@@ -26,11 +26,14 @@ def _worker(rank, world, fused, clip):
     os.environ["SMP_SDP_UNIT_ELEMENTS"] = "250000"
     os.environ["SMP_SDP_FUSED"] = "1" if fused else "0"
     smp.init({"sharded_data_parallel_degree": world, "microbatches": 2, "bf16": True, "ddp": True,
-              "sdp_param_persistence_threshold": 1000, "sdp_gradient_clipping": clip})
+              "sdp_param_persistence_threshold": 1000, "sdp_gradient_clipping": clip,
+              "offload_activations": ckpt_offload})
     dev = torch.device("cuda", smp.local_rank())
     torch.manual_seed(3)
     module = smp.nn.DistributedTransformerLMHead(**CFG)
     oracle = copy.deepcopy(module).to(dev)
+    if ckpt_offload:
+        smp.set_activation_checkpointing(module.transformer.seq_layers, pack_args_as_tuple=True, strategy="each")
     model = smp.DistributedModel(module)
     opt = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=0.01))
     oopt = torch.optim.AdamW(oracle.parameters(), lr=1e-3, weight_decay=0.01)
@@ -65,11 +68,12 @@ def _worker(rank, world, fused, clip):
             "fused_gathers": G.stats.get("sdp_fused_gather", 0)}
 
 
-@pytest.mark.parametrize("fused,clip", [(False, 1.0), (True, 1.0), (True, 0.0)])
-def test_sdp2_gpu_matches_dense(fused, clip):
+@pytest.mark.parametrize("fused,clip,ckpt_offload", [(False, 1.0, False), (True, 1.0, False), (True, 0.0, False),
+                                                     (True, 1.0, True)])
+def test_sdp2_gpu_matches_dense(fused, clip, ckpt_offload):
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    res = run_distributed(_worker, 2, fused, clip, use_cuda=True, timeout=600)
+    res = run_distributed(_worker, 2, fused, clip, ckpt_offload, use_cuda=True, timeout=600)
     for r in res:
         assert r["units"] >= 3
         assert r["worst"] < 2e-2, r
