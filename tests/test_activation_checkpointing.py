@@ -1,0 +1,122 @@
+"""Activation checkpointing on one process (reference test/torch/test_activation_checkpointing.py): smp.checkpoint
+on modules and functions with nested inputs, checkpoint_sequential strategies, RNG preservation with dropout,
+and smp.set_activation_checkpointing applied through DistributedModel."""
+
+import pytest
+import torch
+import torch.nn as nn
+
+import smdistributed_modelparallel_b200 as smp
+from smdistributed_modelparallel_b200.backend.exceptions import CheckpointingConfigError
+from smdistributed_modelparallel_b200.runtime.checkpointing import _chunks, checkpoint, checkpoint_sequential
+
+
+def _mlp(seed, drop=0.0):
+    torch.manual_seed(seed)
+    return nn.Sequential(nn.Linear(16, 32), nn.Tanh(), nn.Dropout(drop), nn.Linear(32, 16))
+
+
+def _grads(model):
+    return [p.grad.clone() for p in model.parameters()]
+
+
+def test_checkpoint_module_matches_plain_backward():
+    m = _mlp(0)
+    x = torch.randn(4, 16, requires_grad=True)
+    m(x).square().sum().backward()
+    ref, refx = _grads(m), x.grad.clone()
+    m.zero_grad()
+    x.grad = None
+    checkpoint(m, x).square().sum().backward()
+    for a, b in zip(ref, _grads(m)):
+        assert torch.allclose(a, b)
+    assert torch.allclose(refx, x.grad)
+
+
+def test_checkpoint_reaches_parameters_when_no_input_needs_grad():
+    m = _mlp(1)
+    x = torch.randn(4, 16)                                   # no grad on the input
+    checkpoint(m, x).sum().backward()
+    assert all(p.grad is not None and p.grad.abs().sum() > 0 for p in m.parameters())
+
+
+def test_checkpoint_nested_inputs_and_outputs():
+    lin = nn.Linear(8, 8)
+
+    def fn(pair, extra=None, flag=True):
+        a, b = pair
+        return {"s": lin(a) + b * extra["w"], "t": (a.sum(), flag)}
+
+    a, b = torch.randn(3, 8, requires_grad=True), torch.randn(3, 8, requires_grad=True)
+    w = torch.randn(3, 8)
+    out = checkpoint(fn, (a, b), extra={"w": w}, flag=False)
+    assert out["t"][1] is False
+    (out["s"].sum() + out["t"][0]).backward()
+    ref = fn((a.detach().requires_grad_(True), b.detach().requires_grad_(True)), extra={"w": w})
+    assert torch.allclose(out["s"], ref["s"])
+    assert torch.allclose(b.grad, w)
+
+
+def test_rng_state_is_replayed_for_dropout():
+    m = _mlp(2, drop=0.5)
+    m.train()
+    x = torch.randn(64, 16, requires_grad=True)
+    torch.manual_seed(123)
+    y = checkpoint(m, x, preserve_rng_state=True)
+    y.sum().backward()                                       # recomputation must draw the same dropout mask
+    g = x.grad.clone()
+    x.grad = None
+    m.zero_grad()
+    torch.manual_seed(123)
+    m(x).sum().backward()
+    assert torch.allclose(g, x.grad)
+
+
+@pytest.mark.parametrize("strategy,expected", [("each", [(0, 1), (1, 2), (2, 3), (3, 4), (4, 5)]),
+                                               ("contiguous", [(0, 5)]), ("group_2", [(0, 2), (2, 4), (4, 5)])])
+def test_sequential_strategies(strategy, expected):
+    assert _chunks(5, strategy) == expected
+    torch.manual_seed(3)
+    seq = nn.Sequential(*[nn.Sequential(nn.Linear(8, 8), nn.Tanh()) for _ in range(5)])
+    x = torch.randn(2, 8, requires_grad=True)
+    seq(x).sum().backward()
+    ref = _grads(seq)
+    seq.zero_grad()
+    checkpoint_sequential(seq, x, strategy=strategy).sum().backward()
+    for a, b in zip(ref, _grads(seq)):
+        assert torch.allclose(a, b)
+
+
+def test_bad_strategy():
+    with pytest.raises(CheckpointingConfigError):
+        _chunks(4, "group_0")
+    with pytest.raises(CheckpointingConfigError):
+        _chunks(4, "every_other")
+    with pytest.raises(CheckpointingConfigError):
+        checkpoint_sequential(nn.Linear(2, 2), torch.zeros(1, 2))
+
+
+def test_set_activation_checkpointing_through_distributed_model():
+    smp.reset()
+    smp.init({"microbatches": 2})
+    torch.manual_seed(4)
+    net = nn.Sequential(nn.Linear(8, 8), nn.Sequential(nn.Linear(8, 8), nn.Tanh(), nn.Linear(8, 8)), nn.Linear(8, 2))
+    ref_net = nn.Sequential(nn.Linear(8, 8), nn.Sequential(nn.Linear(8, 8), nn.Tanh(), nn.Linear(8, 8)), nn.Linear(8, 2))
+    ref_net.load_state_dict(net.state_dict())
+    smp.set_activation_checkpointing(net[1], strategy="contiguous")
+    model = smp.DistributedModel(net)
+    calls = {"n": 0}
+    net[1][0].register_forward_hook(lambda *a: calls.__setitem__("n", calls["n"] + 1))
+
+    @smp.step
+    def train_step(model, x):
+        loss = model(x).square().mean()
+        model.backward(loss)
+        return loss
+
+    x = torch.randn(4, 8)
+    train_step(model, x)
+    assert calls["n"] == 4                                   # 2 microbatches x (forward + recomputation)
+    ref_net(x).square().mean().backward()                    # mean over the batch = mean of the microbatch means
+    for a, b in zip(ref_net.parameters(), model.module.parameters()):
+        assert torch.allclose(a.grad, b.grad, atol=1e-6)
