@@ -176,6 +176,7 @@ class DistributedModel(nn.Module):
                 if self.overlapping_allreduce and not cfg.shard_optimizer_state:
                     self.reducer.install_overlap(
                         self.module, lambda: state.microbatch == state.num_microbatches() - 1)
+                    self.reducer.install_hook_overlap(state.num_microbatches(), lambda: state.microbatch)
         from .runtime.checkpointing import apply_configured_checkpointing
         apply_configured_checkpointing(self.module)
         for hook in list(self._post_partition_hooks.values()):
@@ -263,6 +264,8 @@ class DistributedModel(nn.Module):
         sync = (self._backward_passes % self.backward_passes_per_step) == 0
         if self.reducer is not None:
             self.reducer.require_sync = sync
+            if sync:
+                self.reducer.prepare_for_backward()
         if self.sdp_engine is not None:
             self.sdp_engine._sync_step = sync
         ran_backward = {"v": False}

@@ -170,6 +170,88 @@ class GradReducer:
                     lambda mod, args, _i=idx: mark_inputs(args, lambda: self._bucket_ready(_i))))
         return len(self.buckets)
 
+    # ------------------------------------------------------------------ overlap, plain .grad tensors (fp32 training)
+    def install_hook_overlap(self, num_microbatches, current_microbatch):
+        """Without a GradBuffer gradients arrive as ordinary ``.grad`` tensors, one accumulation per parameter
+        per microbatch.  Readiness is tracked by the native gradient counter (csrc/core/runtime.cpp,
+        ``smpc_gc_*``: a parameter is final when the last expected contribution of the last microbatch has
+        landed - the contract of the reference's ``GradCounter``) and parameters are grouped by
+        the native bucket planner (``smpc_plan_buckets``; 1 MB first bucket, then ``bucket_cap_mb``) in reverse
+        parameter order, i.e. roughly the order backward produces them.  A full bucket is flattened and
+        all-reduced asynchronously; ``synchronize`` waits, copies back and reduces whatever was never final
+        (unused parameters)."""
+        import ctypes
+
+        from ..backend import native_core
+
+        if self.grad_buffer is not None or self.dp_size == 1 or not self.params:
+            return 0
+        lib = native_core.load()
+        self._lib = lib
+        self._num_mb, self._cur_mb = int(num_microbatches), current_microbatch
+        order = list(reversed(self.params))
+        n = len(order)
+        nbytes = (ctypes.c_longlong * n)(*[p.numel() * p.element_size() for p in order])
+        # parameters reduced over different groups (scaled-batch vs the rest) or of different dtypes never share a bucket
+        dtypes = {}
+        keys = (ctypes.c_int * n)(*[dtypes.setdefault((p.dtype, bool(is_scaled_batch_parameter(p))), len(dtypes))
+                                    for p in order])
+        bucket_of = (ctypes.c_int * n)()
+        nb = lib.smpc_plan_buckets(n, nbytes, keys, 1 << 20, self.bucket_elems * 4, bucket_of)
+        self._hook_buckets = [{"params": [], "pending": 0, "work": None, "flat": None} for _ in range(nb)]
+        self._param_bucket = {}
+        self._param_id = {}
+        for i, p in enumerate(order):
+            self._hook_buckets[bucket_of[i]]["params"].append(p)
+            self._param_bucket[p] = bucket_of[i]
+            self._param_id[p] = i
+        self._gc = lib.smpc_gc_create(n, self._num_mb)
+        self._ids = (ctypes.c_int * n)(*range(n))
+        for p in order:
+            self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
+        return nb
+
+    def prepare_for_backward(self):
+        """Start of a synchronising step: every parameter is expected once per microbatch."""
+        if getattr(self, "_gc", None) is None:
+            return
+        self._lib.smpc_gc_clear(self._gc)
+        for mb in range(self._num_mb):
+            self._lib.smpc_gc_increment_expected(self._gc, mb, self._ids, len(self._ids))
+            self._lib.smpc_gc_mark_fwd_done(self._gc, mb)   # expectations are announced up front, not per forward
+        for b in self._hook_buckets:
+            b["pending"], b["work"], b["flat"] = len(b["params"]), None, None
+
+    def _on_grad(self, p):
+        if getattr(self, "_gc", None) is None or not self.require_sync or self.comm_hook is not None:
+            return
+        self._lib.smpc_gc_set_microbatch(self._gc, int(self._cur_mb()))
+        if self._lib.smpc_gc_mark_grad_computed(self._gc, self._param_id[p]) != 1:
+            return                                     # not the last contribution of the last microbatch yet
+        b = self._hook_buckets[self._param_bucket[p]]
+        b["pending"] -= 1
+        if b["pending"] == 0:
+            group = self.rdp_group if is_scaled_batch_parameter(b["params"][0]) else self.dp_group
+            if group is None or dist.get_world_size(group) == 1:
+                return
+            b["flat"] = torch.cat([q.grad.reshape(-1) for q in b["params"]])
+            b["work"] = dist.all_reduce(b["flat"], group=group, async_op=True)
+            self.stats["overlapped_elems"] += b["flat"].numel()
+
+    def _finish_hook_overlap(self, scale):
+        done = set()
+        for b in self._hook_buckets:
+            if b["work"] is None:
+                continue
+            b["work"].wait()
+            off = 0
+            for q in b["params"]:
+                q.grad.copy_(b["flat"][off:off + q.numel()].view_as(q.grad)).mul_(scale)
+                off += q.numel()
+                done.add(q)
+            b["work"], b["flat"] = None, None
+        return done
+
     def _group_of(self, region):
         return self.rdp_group if region == "scaled_batch" else self.dp_group
 
@@ -221,8 +303,11 @@ class GradReducer:
             self._finish_overlapped()
             self.grad_buffer.buffer.mul_(scale)
             return
+        done = self._finish_hook_overlap(scale) if getattr(self, "_gc", None) is not None else set()
         for want_scaled, group in ((True, self.rdp_group), (False, self.dp_group)):
-            grads = [p.grad for p in self.params if p.grad is not None and is_scaled_batch_parameter(p) == want_scaled]
+            grads = [p.grad for p in self.params
+                     if p.grad is not None and p not in done and is_scaled_batch_parameter(p) == want_scaled]
+            self.stats["tail_elems"] += sum(g.numel() for g in grads)
             by_dtype = {}
             for g in grads:
                 by_dtype.setdefault(g.dtype, []).append(g)

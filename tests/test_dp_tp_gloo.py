@@ -59,6 +59,9 @@ def test_dp2_matches_dense(shard, bf16):
     tol = 4e-3 if not bf16 else 5e-2
     for r in res:
         assert r["worst"] < tol, r
+        if not bf16 and not shard:
+            # fp32 training: per-parameter hooks + native gradient counter + planned buckets reduce during backward
+            assert r["stats"]["overlapped_elems"] > 0, r
         if bf16 and not shard:
             # 16-bit training without optimizer-state sharding: the two layers are reduced while backward runs
             assert r["buckets"] == 2 and r["stats"]["overlapped_elems"] > 0 and r["stats"]["tail_elems"] > 0, r
