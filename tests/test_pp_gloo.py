@@ -138,3 +138,49 @@ def test_pp2_tp2_tracks_dense(window):
         oopt.step()
         mean = sum(r["losses"][it] for r in res if r["pp_rank"] == 0) / 2
         assert abs(mean - ol.item()) < 2e-4, (it, mean, ol.item())
+
+
+def _pp4_worker(rank, world):
+    import copy
+
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"pipeline_parallel_degree": 4, "microbatches": 4, "ddp": False, "active_microbatches": 3})
+    torch.manual_seed(7)
+    cfg = dict(CFG, num_layers=8)
+    module = smp.nn.DistributedTransformerLMHead(**cfg)
+    oracle = copy.deepcopy(module)
+    model = smp.DistributedModel(module)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    torch.manual_seed(11)
+    ids = torch.randint(0, cfg["vocab_size"], (8, 16))
+    opt.zero_grad()
+    loss = train_step(model, ids).reduce_mean().item()
+    ol, _ = oracle((ids, None, None, None, ids))
+    ol.backward()
+    ref = {n: p.grad for n, p in oracle.named_parameters()}
+    worst, n_local = 0.0, 0
+    for n, p in model.local_named_parameters():
+        worst = max(worst, (p.grad - ref[n]).abs().max().item())
+        n_local += 1
+    layers = [smp.state.module_manager.get_partition(l) for l in model.module.transformer.seq_layers]
+    return {"loss": loss, "oracle": ol.item(), "worst": worst, "n_local": n_local, "layers": layers}
+
+
+def test_pp4_matches_dense():
+    """Four pipeline stages (reference test/torch/mpi_4ps): the layer stack is cut into four contiguous chunks
+    served in sequence; loss and every local gradient match the dense model."""
+    res = run_distributed(_pp4_worker, 4, timeout=420)
+    for r in res:
+        assert abs(r["loss"] - r["oracle"]) < 1e-5, r
+        assert r["worst"] < 1e-5, r
+        assert r["n_local"] > 0
+    layers = res[0]["layers"]
+    assert sorted(set(layers)) == [0, 1, 2, 3] and layers == sorted(layers), layers
