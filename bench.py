@@ -56,7 +56,8 @@ def parse():
 def reference_arm(args):
     why = ("reference is an unpacked cp38 binary wheel with no setup.py/pyproject and all five native libraries "
            "(smplib.so, smp_torch_cuda_lib.so, amp_C.so, ...) absent; pip install of /root/reference fails: not installable")
-    print(json.dumps({"impl": "reference", "unavailable": why}))
+    if int(os.environ.get("RANK", "0")) == 0:          # one line per job, also under torchrun
+        print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
     return 0
 
 
