@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--checkpoint", type=int, default=-1, help="activation checkpointing (1/0, default auto)")
     ap.add_argument("--active-microbatches", type=int, default=0, help="pipeline window (default: config default)")
     ap.add_argument("--offload", type=int, default=0, help="offload checkpointed activations to pinned host memory")
+    ap.add_argument("--fp16", type=int, default=0, help="fp16 with dynamic loss scaling instead of bf16")
+    ap.add_argument("--shard-optimizer-state", type=int, default=0, help="ZeRO-1 style optimizer-state sharding over dp")
     ap.add_argument("--layers", type=int, default=0, help="debug only: override layer count (marks the run invalid)")
     return ap.parse_args()
 
@@ -258,7 +260,9 @@ def main():
     nmb = args.microbatches or (2 if pp == 1 else 8)
     baseline = args.impl == "baseline"
 
-    conf = {"microbatches": nmb, "bf16": True, "pipeline_parallel_degree": pp, "tensor_parallel_degree": tp,
+    half = torch.float16 if args.fp16 else torch.bfloat16
+    conf = {"microbatches": nmb, "bf16": not args.fp16, "fp16": bool(args.fp16),
+            "shard_optimizer_state": bool(args.shard_optimizer_state), "pipeline_parallel_degree": pp, "tensor_parallel_degree": tp,
             "ddp": n > 1, "delayed_parameter_initialization": True, "pipeline": "interleaved"}
     if sdp > 1:
         conf["sharded_data_parallel_degree"] = sdp
@@ -275,14 +279,15 @@ def main():
     dev = torch.device("cuda", smp.local_rank())
     torch.manual_seed(1234 + smp.rank())
 
-    with smp.model_creation(tensor_parallelism=tp > 1, dtype=torch.bfloat16):
+    with smp.model_creation(tensor_parallelism=tp > 1, dtype=half):
         module = smp.nn.DistributedTransformerLMHead(**mcfg)
     use_ckpt = args.checkpoint if args.checkpoint >= 0 else (1 if args.model == "gpt-neox-20b" else 0)
     if use_ckpt:
         smp.set_activation_checkpointing(module.transformer.seq_layers, pack_args_as_tuple=True, strategy="each")
     model = smp.DistributedModel(module)
     optimizer = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-4, betas=(0.9, 0.95),
-                                                           weight_decay=0.1))
+                                                           weight_decay=0.1),
+                                         dynamic_loss_scale=bool(args.fp16))
 
     @smp.step
     def train_step(model, ids):
@@ -362,17 +367,17 @@ def main():
         e2e = tokens_per_step / (ms_b / 1000)
         flops = train_flops_per_token(mcfg, seq) * (4.0 / 3.0 if use_ckpt else 1.0)
         line = {
-            "metric": f"training tokens/sec (device-timed, max over ranks), {METRIC_NAMES.get(args.model, args.model)} bf16 seq {seq}",
+            "metric": f"training tokens/sec (device-timed, max over ranks), {METRIC_NAMES.get(args.model, args.model)} {'fp16' if args.fp16 else 'bf16'} seq {seq}",
             "value": round(value, 1), "unit": "tokens/s", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms_a, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic tokens, random-init weights",
+            "dtype": "fp16" if args.fp16 else "bf16", "data": "synthetic tokens, random-init weights",
             "impl": "baseline-nccl-cublas" if baseline else "b200",
             "config": {"model": args.model, "params": param_count(mcfg), "layers": mcfg["num_layers"],
                        "global_batch": global_batch, "seq_len": seq, "microbatches": nmb, "micro_batch": micro,
                        "parallelism": label, "tp_comm": tp_ops.get_comm_mode() if tp > 1 else None, "activation_checkpointing": bool(use_ckpt), "offload_activations": bool(args.offload),
                        "active_microbatches": conf.get("active_microbatches", nmb) if pp > 1 else None,
-                       "optimizer": "AdamW fp32 master",
-                       "l2": "working set (12 GB of bf16 weights per step) >> 126 MB L2; no explicit flush needed",
+                       "optimizer": "AdamW fp32 master" + (", state sharded over dp" if args.shard_optimizer_state else ""),
+                       "l2": f"working set ({2 * param_count(mcfg) / 2 ** 30:.1f} GiB of 16-bit weights read per pass) >> 126 MB L2; no explicit flush needed",
                        "valid": not bool(args.layers)},
             "model_tflops_per_gpu": round(value * flops / n / 1e12, 1),
             "clocks": clocks,
