@@ -20,6 +20,7 @@ Execution differs from the reference by design (B200-first):
 from __future__ import annotations
 
 import math
+import os
 from collections import OrderedDict
 
 import torch
@@ -57,6 +58,10 @@ def _group():
 
 
 def _gelu_mode(activation: str):
+    # SMP_USE_HF_GELU=1 (reference torch/nn/transformer.py:994): plain torch GELU after the GEMM instead of the
+    # GELU folded into the GEMM epilogue - a debugging switch for bit-comparisons with HuggingFace
+    if os.environ.get("SMP_USE_HF_GELU") == "1":
+        return None
     if activation == "gelu":
         return "erf"
     if activation in _TANH_ACTS:

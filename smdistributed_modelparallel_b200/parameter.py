@@ -13,6 +13,8 @@ from __future__ import annotations
 
 from contextlib import contextmanager
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -60,6 +62,15 @@ def _materialize_module(m: nn.Module, device):
     for name, b in list(m.named_buffers(recurse=False)):
         if b.is_meta:
             m._buffers[name] = torch.empty(b.shape, dtype=b.dtype, device=device)
+    # SMP_USE_FLOAT32_INIT=1 (reference torch/parameter.py:20): run the initialisers on fp32 storage and round
+    # once, so 16-bit models start from the same values as their fp32 counterparts
+    fp32_init = os.environ.get("SMP_USE_FLOAT32_INIT", "0") not in ("0", "", "false")
+    lowp = {}
+    if fp32_init:
+        for name, p in list(m.named_parameters(recurse=False)):
+            if p.dtype in (torch.float16, torch.bfloat16):
+                lowp[name] = p.dtype
+                p.data = p.data.float()
     custom = getattr(m, "_smp_custom_init", None)
     if custom is not None:
         custom(m)
@@ -73,6 +84,8 @@ def _materialize_module(m: nn.Module, device):
                 nn.init.normal_(p, 0.0, 0.02)
             else:
                 nn.init.zeros_(p)
+    for name, dt in lowp.items():
+        m._parameters[name].data = m._parameters[name].data.to(dt)
     return True
 
 
