@@ -126,3 +126,31 @@ def _bus_worker(rank, world):
 
 def test_message_bus_two_processes():
     assert all(run_distributed(_bus_worker, 2))
+
+
+def _failure_worker(rank, world):
+    import time
+
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200.backend.collectives import RankType
+    from smdistributed_modelparallel_b200.backend.exceptions import SMPRuntimeError
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2})
+    if rank == 1:
+        time.sleep(0.5)
+        smp.state.core.shutdown(success=False)            # what the exit hook does when this rank dies
+        return "failed-on-purpose"
+    t0 = time.time()
+    try:
+        smp.state.comm.recv_from(1, RankType.WORLD_RANK)   # would block forever without failure propagation
+    except SMPRuntimeError as e:
+        return f"aborted after {time.time() - t0:.1f}s: {e}"
+    return "received?"
+
+
+def test_peer_failure_aborts_blocking_receive():
+    """Failure propagation (reference backend/core.py:165-188,227-232; test/backend/shutdown_test.py): a rank that
+    shuts down unsuccessfully makes its peers' blocking receives raise instead of hanging."""
+    res = run_distributed(_failure_worker, 2, timeout=120)
+    assert res[1] == "failed-on-purpose"
+    assert res[0].startswith("aborted"), res[0]
