@@ -83,6 +83,14 @@ def reset():
     state.tp_registry.reset()
     state.init_model_specific_state()
     state.step_func = {}
+    # device-side caches of the op wrappers (scratch buffers, rotary tables, deferred gathers)
+    from .ops import attention as _attention
+    from .ops import workspace as _workspace
+    from .ops._sdp_hook import pending_gathers as _pending
+
+    _workspace.release_all()
+    _attention._table_cache.clear()
+    _pending.clear()
 
 
 def shutdown():
