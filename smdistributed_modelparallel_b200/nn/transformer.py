@@ -222,8 +222,17 @@ class DistributedAttentionLayer(DistributedModule):
         if self.scale_attn_by_layer_idx and not self.query_key_layer_scaling:
             scale = scale / float(self.layer_idx + 1)
         mask = attention_mask if (attention_mask is not None and not causal) else None
+        # query_key_layer_scaling / attention_in_fp32: keep the stored 16-bit scores small - the score GEMM applies
+        # 1/sqrt(d) (and 1/(layer+1)); the softmax, which works in fp32, undoes the layer factor.  The accumulation
+        # itself is always fp32 (TMEM).
+        gemm_scale = 1.0
+        if self.query_key_layer_scaling or self.attention_in_fp32:
+            gemm_scale = 1.0 / math.sqrt(d) if self.scale_attention_scores else 1.0
+            if self.query_key_layer_scaling and self.scale_attn_by_layer_idx:
+                gemm_scale /= float(self.layer_idx + 1)
         ctx = A.core_attention(q, k, v, causal=causal, mask=mask, scale=scale, dropout_p=self.attention_dropout_prob,
-                               training=self.training, window=self.window_size if causal else None)
+                               training=self.training, window=self.window_size if causal else None,
+                               gemm_scale=gemm_scale)
         return A.heads_to_tokens(ctx).reshape(B * S, la)
 
     def forward(self, inp):

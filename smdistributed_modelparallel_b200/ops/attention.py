@@ -190,12 +190,12 @@ class _CausalAttention(torch.autograd.Function):
     non-zero part - about 44 % of the attention FLOPs and score traffic at S = 2048."""
 
     @staticmethod
-    def forward(ctx, q, k, v, scale):
+    def forward(ctx, q, k, v, scale, gemm_scale=1.0):
         from .gemm import gemm
 
         BH, S, d = q.shape
         scores = torch.empty(BH, S, S, dtype=q.dtype, device=q.device)
-        gemm(q, k, out=scores, causal="lower_out")
+        gemm(q, k, out=scores, causal="lower_out", alpha=gemm_scale)    # stored scores = gemm_scale * q k^T
         probs = torch.empty_like(scores)
         N.count_launch()
         N.call("smpk_softmax_fwd", N.stream_ptr(q.device), scores.data_ptr(), probs.data_ptr(), N.dtype_code(q.dtype),
@@ -203,7 +203,7 @@ class _CausalAttention(torch.autograd.Function):
         del scores
         out = gemm(probs, v, b_mn_major=True, causal="lower_a")
         ctx.save_for_backward(q, k, v, probs)
-        ctx.scale = scale
+        ctx.scale, ctx.gemm_scale = scale, gemm_scale
         return out
 
     @staticmethod
@@ -221,9 +221,10 @@ class _CausalAttention(torch.autograd.Function):
         N.call("smpk_softmax_bwd", N.stream_ptr(q.device), dp.data_ptr(), probs.data_ptr(), ds.data_ptr(),
                N.dtype_code(q.dtype), 2, float(ctx.scale), BH, S, S)
         del dp
-        dq = gemm(ds, k, b_mn_major=True, causal="lower_a")                              # dS K
-        dk = gemm(ds, q, a_mn_major=True, b_mn_major=True, causal="lower_at")            # dS^T Q
-        return dq, dk, dv, None
+        a = ctx.gemm_scale
+        dq = gemm(ds, k, b_mn_major=True, causal="lower_a", alpha=a)                     # dS K
+        dk = gemm(ds, q, a_mn_major=True, b_mn_major=True, causal="lower_at", alpha=a)   # dS^T Q
+        return dq, dk, dv, None, None
 
 
 def _causal_fast_path(q, k, mask, window, dropout_p, training) -> bool:
@@ -234,20 +235,24 @@ def _causal_fast_path(q, k, mask, window, dropout_p, training) -> bool:
 
 # --------------------------------------------------------------------------------- core attention
 def core_attention(q, k, v, *, causal: bool = True, mask=None, scale: float | None = None, dropout_p: float = 0.0,
-                   training: bool = True, window: int | None = None):
+                   training: bool = True, window: int | None = None, gemm_scale: float = 1.0):
     """softmax(scale * q k^T + mask) v for q,k,v [B, heads, S, d]; returns [B, heads, Sq, d].
 
     ``mask`` is a uint8/bool [B,1,Sq,Sk] tensor whose non-zero entries are excluded; ``causal`` applies
-    the lower-triangular mask; ``window`` (local attention) is folded into the byte mask.
+    the lower-triangular mask; ``window`` (local attention) is folded into the byte mask.  ``gemm_scale`` is the
+    part of ``scale`` applied by the score GEMM itself (the stored 16-bit scores are ``gemm_scale * q k^T``, the
+    softmax applies the rest) - the reference's ``query_key_layer_scaling`` / ``attention_in_fp32`` guard against
+    fp16 overflow of the raw scores (reference torch/nn/transformer.py:1769-1835).
     """
     B, h, Sq, d = q.shape
     Sk = k.shape[2]
     scale = (1.0 / math.sqrt(d)) if scale is None else scale
     if causal and _causal_fast_path(q, k, mask, window, dropout_p, training):
         ctx = _CausalAttention.apply(q.reshape(B * h, Sq, d).contiguous(), k.reshape(B * h, Sk, d).contiguous(),
-                                     v.reshape(B * h, Sk, d).contiguous(), float(scale))
+                                     v.reshape(B * h, Sk, d).contiguous(), float(scale / gemm_scale), float(gemm_scale))
         return ctx.reshape(B, h, Sq, d)
-    scores = bmm_nt(q.reshape(B * h, Sq, d), k.reshape(B * h, Sk, d))
+    scores = bmm_nt(q.reshape(B * h, Sq, d), k.reshape(B * h, Sk, d), alpha=gemm_scale)
+    scale = scale / gemm_scale
     if window is not None:
         i = torch.arange(Sq, device=q.device)[:, None] + (Sk - Sq)
         j = torch.arange(Sk, device=q.device)[None, :]

@@ -325,6 +325,13 @@ def test_causal_attention_triangular_gemms(B, h, S, d):
     _report("causal attention dq", dq, rq, 3e-2)
     _report("causal attention dk", dk, rk, 3e-2)
     _report("causal attention dv", dv, rv, 3e-2)
+    # same result when the score GEMM applies the 1/sqrt(d) itself (query_key_layer_scaling / attention_in_fp32)
+    o2 = A.core_attention(q, k, v, causal=True, gemm_scale=1.0 / d ** 0.5)
+    dq2, dk2, dv2 = torch.autograd.grad(o2, (q, k, v), go)
+    _report("causal attention out (scaled in GEMM)", o2, of, 2e-2)
+    _report("causal attention dq (scaled in GEMM)", dq2, rq, 3e-2)
+    _report("causal attention dk (scaled in GEMM)", dk2, rk, 3e-2)
+    _report("causal attention dv (scaled in GEMM)", dv2, rv, 3e-2)
 
 
 @pytest.mark.parametrize("act", ["tanh", "erf"])
