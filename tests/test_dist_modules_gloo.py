@@ -60,6 +60,25 @@ def _worker(rank, world):
     out["layer_heads"] = layer.attention.local_attention_heads
     model = smp.DistributedModel(layer)
     out["layer_sd"] = {k: v.clone() for k, v in model.state_dict().items()}     # gathered over tp
+    # ---- decoder layer with cross attention over encoder states of a different length, post-LayerNorm
+    smp.reset()
+    torch.manual_seed(2)
+    with smp.tensor_parallelism(enabled=True):
+        xl = smp.nn.DistributedTransformerLayer(num_attention_heads=4, attention_head_size=4, hidden_size=16,
+                                                intermediate_size=24, attention_dropout_prob=0.0,
+                                                hidden_dropout_prob=0.0, activation="relu", pre_layernorm=False,
+                                                post_layernorm=True, causal_mask_size=8, add_cross_attention=True,
+                                                use_normal_initialization=True)
+    d_all = torch.randn(4, 8, 16, generator=data)
+    enc_all = torch.randn(4, 6, 16, generator=data)
+    dh = d_all[rank * 2:(rank + 1) * 2].clone().requires_grad_(True)
+    enc = enc_all[rank * 2:(rank + 1) * 2].clone().requires_grad_(True)
+    yx = xl((dh, None, enc, None))[0]
+    yx.square().sum().backward()
+    out["x_y"], out["x_dh"], out["x_denc"] = yx.detach(), dh.grad.clone(), enc.grad.clone()
+    out["d_all"], out["enc_all"] = d_all, enc_all
+    xm = smp.DistributedModel(xl)
+    out["x_sd"] = {k: v.clone() for k, v in xm.state_dict().items()}
     return out
 
 
@@ -114,3 +133,18 @@ def test_tp2_modules_match_dense():
     for r, rr in enumerate(res):
         assert torch.allclose(rr["layer_y"], yd[r * 2:(r + 1) * 2].detach(), atol=2e-5)
         assert torch.allclose(rr["layer_dx"], ha.grad[r * 2:(r + 1) * 2], atol=2e-5)
+    # cross-attention decoder layer
+    xdense = DistributedTransformerLayer(num_attention_heads=4, attention_head_size=4, hidden_size=16,
+                                         intermediate_size=24, attention_dropout_prob=0.0, hidden_dropout_prob=0.0,
+                                         activation="relu", pre_layernorm=False, post_layernorm=True, causal_mask_size=8,
+                                         add_cross_attention=True, use_normal_initialization=True)
+    missing = xdense.load_state_dict(r0["x_sd"], strict=False)
+    assert not missing.missing_keys, missing
+    da = r0["d_all"].clone().requires_grad_(True)
+    ea = r0["enc_all"].clone().requires_grad_(True)
+    yd = xdense((da, None, ea, None))[0]
+    yd.square().sum().backward()
+    for r, rr in enumerate(res):
+        assert torch.allclose(rr["x_y"], yd[r * 2:(r + 1) * 2].detach(), atol=2e-5)
+        assert torch.allclose(rr["x_dh"], da.grad[r * 2:(r + 1) * 2], atol=2e-5)
+        assert torch.allclose(rr["x_denc"], ea.grad[r * 2:(r + 1) * 2], atol=2e-5)
