@@ -19,6 +19,16 @@ def _worker(rank, world, family):
         from transformers import GPT2Config, GPT2LMHeadModel as Cls
         cfg = GPT2Config(n_layer=2, n_head=4, n_embd=32, n_positions=32, vocab_size=96, resid_pdrop=0, embd_pdrop=0,
                          attn_pdrop=0)
+    elif family == "gptneox":
+        from transformers import GPTNeoXConfig, GPTNeoXForCausalLM as Cls
+        cfg = GPTNeoXConfig(num_hidden_layers=2, num_attention_heads=4, hidden_size=32, intermediate_size=64,
+                            max_position_embeddings=32, vocab_size=96, rotary_pct=0.5, hidden_dropout=0.0,
+                            attention_dropout=0.0)
+    elif family == "gptneo":
+        from transformers import GPTNeoConfig, GPTNeoForCausalLM as Cls
+        cfg = GPTNeoConfig(num_layers=2, num_heads=4, hidden_size=32, max_position_embeddings=32, vocab_size=96,
+                           attention_types=[[["global", "local"], 1]], window_size=8, resid_dropout=0, embed_dropout=0,
+                           attention_dropout=0)
     else:
         from transformers import GPTJConfig, GPTJForCausalLM as Cls
         cfg = GPTJConfig(n_layer=2, n_head=4, n_embd=32, n_positions=32, vocab_size=96, rotary_dim=4, resid_pdrop=0,
@@ -49,7 +59,7 @@ def _worker(rank, world, family):
     return {"ref": ref, "loss": loss, "replaced": replaced, "worst": worst, "missing": missing, "qkv": local_qkv}
 
 
-@pytest.mark.parametrize("family", ["gpt2", "gptj"])
+@pytest.mark.parametrize("family", ["gpt2", "gptj", "gptneox", "gptneo"])
 def test_hf_model_under_tp2(family):
     res = run_distributed(_worker, 2, family, timeout=300)
     assert all(r["replaced"] == "DistributedTransformerLMHead" for r in res)
