@@ -431,19 +431,7 @@ class DistributedModel(nn.Module):
             return self.sdp_engine._model_shard_dict()
         full = self.module.state_dict(prefix=prefix + "module.", keep_vars=keep_vars)
         if state.core.pp_size() > 1:
-            local_prefixes = []
-            for n, m in self.module.named_modules():
-                if self._is_local_module(m):
-                    local_prefixes.append(prefix + "module." + (n + "." if n else ""))
-            def is_local(k):
-                best = max((p for p in local_prefixes if k.startswith(p)), key=len, default=None)
-                if best is None:
-                    return False
-                rest = k[len(best):]
-                return "." not in rest or True
-            nonlocal_ids = {id(t) for t in list(self.module.parameters()) + list(self.module.buffers())
-                            if getattr(t, "_smp_nonlocal", False)}
-            full = OrderedDict((k, v) for k, v in full.items() if v.numel() > 0 or id(v) not in nonlocal_ids)
+            # tensors of modules living on other pipeline ranks were released to empty storage at partition time
             full = OrderedDict((k, v) for k, v in full.items() if v.numel() > 0)
         sd = destination if destination is not None else OrderedDict()
         for k, v in full.items():
