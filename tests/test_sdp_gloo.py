@@ -16,13 +16,13 @@ CFG = dict(num_layers=2, num_attention_heads=4, attention_head_size=8, hidden_si
            post_layernorm=False, final_layernorm=True, use_normal_initialization=True)
 
 
-def _worker(rank, world, bf16, ckpt_dir, act_ckpt):
+def _worker(rank, world, bf16, ckpt_dir, act_ckpt, degree=2):
     import copy
 
     import smdistributed_modelparallel_b200 as smp
 
     os.environ["SMP_SDP_UNIT_ELEMENTS"] = "9000"      # small units so the toy model splits into several
-    smp.init({"sharded_data_parallel_degree": 2, "microbatches": 2, "bf16": bf16, "ddp": True,
+    smp.init({"sharded_data_parallel_degree": degree, "microbatches": 2, "bf16": bf16, "ddp": True,
               "sdp_param_persistence_threshold": 100, "sdp_gradient_clipping": 1.0})
     torch.manual_seed(3)
     module = smp.nn.DistributedTransformerLMHead(**CFG)
@@ -83,3 +83,17 @@ def test_sdp2_matches_dense_and_checkpoints(bf16, act_ckpt):
         assert r["roundtrip"] < 1e-6
         assert r["uc"] == {"it": 4}
     assert {"model_0.pt", "model_1.pt", "optimizer_0.pt", "optimizer_1.pt", "smp_config.pt", "user_content.pt"} <= set(res[0]["files"])
+
+
+def test_sdp_degree2_with_two_replica_groups():
+    """Four ranks, shard groups of two: gradients are reduce-scattered inside a shard group and all-reduced across
+    the replica groups; parameters still track the dense model trained on all four ranks' batches, and only the
+    first replica of each shard index writes checkpoint files."""
+    with tempfile.TemporaryDirectory() as d:
+        res = run_distributed(_worker, 4, False, d, False, 2, timeout=420)
+    for r in res:
+        assert r["worst"] < 2e-3, r["worst"]
+        assert r["roundtrip"] < 1e-6
+    files = set(res[0]["files"])
+    assert {"model_0.pt", "model_1.pt", "optimizer_0.pt", "optimizer_1.pt"} <= files
+    assert not any(f.startswith("model_2") or f.startswith("model_3") for f in files)
