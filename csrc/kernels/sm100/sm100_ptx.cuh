@@ -135,6 +135,10 @@ __device__ __forceinline__ void fence_mbar_init_cluster() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
 // TMA load issued by either CTA of the pair; the bytes are counted on the LEADER's barrier at the same offset.
+// Not a multicast load: each CTA fills its own shared memory.  Every tensor map in this library covers this GPU's
+// own memory only - data of other GPUs is brought in by ordinary loads (copy warps) before any TMA touches it;
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+// memory hung the GPU.
 __device__ __forceinline__ void tma_load_3d_2sm(void* smem_dst, const void* desc, uint64_t* bar, int c0, int c1,
                                                 int c2) {
   asm volatile(
