@@ -207,6 +207,7 @@ class GradReducer:
             self._param_id[p] = i
         self._gc = lib.smpc_gc_create(n, self._num_mb)
         self._ids = (ctypes.c_int * n)(*range(n))
+        self._contrib = {}            # param id -> accumulations per microbatch, when more than one
         for p in order:
             self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
         return nb
@@ -215,22 +216,39 @@ class GradReducer:
         """Start of a synchronising step: every parameter is expected once per microbatch."""
         if getattr(self, "_gc", None) is None:
             return
+        import ctypes
+
         self._lib.smpc_gc_clear(self._gc)
+        # a parameter normally receives one accumulation per microbatch; one that is differentiated in several
+        # backward segments (a tied embedding under pipeline parallelism, several model.backward calls) receives
+        # more - learnt from the step in which the surplus was first seen (that step's bucket is reduced at the end)
+        ids = [i for i in range(len(self._ids)) for _ in range(self._contrib.get(i, 1))]
+        arr = (ctypes.c_int * len(ids))(*ids)
         for mb in range(self._num_mb):
-            self._lib.smpc_gc_increment_expected(self._gc, mb, self._ids, len(self._ids))
+            self._lib.smpc_gc_increment_expected(self._gc, mb, arr, len(ids))
             self._lib.smpc_gc_mark_fwd_done(self._gc, mb)   # expectations are announced up front, not per forward
+        self._seen_now = {}
         for b in self._hook_buckets:
-            b["pending"], b["work"], b["flat"] = len(b["params"]), None, None
+            b["pending"], b["work"], b["flat"], b["dirty"] = len(b["params"]), None, None, False
 
     def _on_grad(self, p):
         if getattr(self, "_gc", None) is None or not self.require_sync or self.comm_hook is not None:
             return
-        self._lib.smpc_gc_set_microbatch(self._gc, int(self._cur_mb()))
-        if self._lib.smpc_gc_mark_grad_computed(self._gc, self._param_id[p]) != 1:
-            return                                     # not the last contribution of the last microbatch yet
+        mb = int(self._cur_mb())
+        pid = self._param_id[p]
+        self._lib.smpc_gc_set_microbatch(self._gc, mb)
+        rc = self._lib.smpc_gc_mark_grad_computed(self._gc, pid)
+        n = self._seen_now[(mb, pid)] = self._seen_now.get((mb, pid), 0) + 1
         b = self._hook_buckets[self._param_bucket[p]]
+        if rc == -2:
+            # more contributions than announced: whatever was (or will be) sent for this bucket is incomplete
+            b["dirty"] = True
+            self._contrib[pid] = max(self._contrib.get(pid, 1), n)
+            return
+        if rc != 1:
+            return                                     # not the last contribution of the last microbatch yet
         b["pending"] -= 1
-        if b["pending"] == 0:
+        if b["pending"] == 0 and not b["dirty"]:
             group = self.rdp_group if is_scaled_batch_parameter(b["params"][0]) else self.dp_group
             if group is None or dist.get_world_size(group) == 1:
                 return
@@ -244,6 +262,9 @@ class GradReducer:
             if b["work"] is None:
                 continue
             b["work"].wait()
+            if b["dirty"]:                             # reduced too early: redo from the complete .grad at the end
+                b["work"], b["flat"] = None, None
+                continue
             off = 0
             for q in b["params"]:
                 q.grad.copy_(b["flat"][off:off + q.numel()].view_as(q.grad)).mul_(scale)
