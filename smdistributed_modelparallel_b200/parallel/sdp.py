@@ -283,6 +283,8 @@ class ShardedDataParallelEngine:
                 self._order.append(u)
             if self._in_backward:
                 u.recompute_seen = True
+            else:
+                u.calls_in_mb = getattr(u, "calls_in_mb", 0) + 1
             self._ensure(u, lazy_ok=True)
             u.users += 1
         if not self._in_backward:            # a recomputed forward must not prefetch units that are already done
@@ -360,6 +362,8 @@ class ShardedDataParallelEngine:
             return None
         if self.state.microbatch != self.state.num_microbatches() - 1 or not self._sync_step:
             return None
+        if getattr(u, "calls_in_mb", 1) > 1:
+            return None                      # a reused module is reduced once per use: the update must wait for all
         group = opt.param_groups[u.gi]
         if group.get("amsgrad", False) or group.get("maximize", False):
             return None
@@ -384,6 +388,8 @@ class ShardedDataParallelEngine:
     # ------------------------------------------------------------------ DistributedModel entry points
     def forward(self, module, args, kwargs):
         self._build()
+        for u in self.units:
+            u.calls_in_mb = 0
         out = module(*args, **kwargs)
         if not self._order_frozen and self._order:
             self._order_frozen = True
