@@ -47,6 +47,20 @@ class TwoHeads(nn.Module):
         return self.h1(t) * scale, {"aux": self.h2(t)}
 
 
+class Unused(nn.Module):
+    """A child that never runs and an input that is ignored (the reference documents both as unsupported graphs,
+    test/torch/mpi/xfails; here they simply produce no gradient)."""
+
+    def __init__(self):
+        super().__init__()
+        self.a = nn.Sequential(nn.Linear(8, 8), nn.Tanh())
+        self.dead = nn.Linear(8, 8)
+        self.b = nn.Linear(8, 3)
+
+    def forward(self, x, ignored=None):
+        return self.b(self.a(x))
+
+
 def _build(kind, smp=None):
     torch.manual_seed(11)
     if kind == "reuse":
@@ -57,6 +71,12 @@ def _build(kind, smp=None):
             smp.set_partition(net.out, 1)
     elif kind == "buffers":
         net = WithBuffers()
+    elif kind == "unused":
+        net = Unused()
+        if smp is not None:
+            smp.set_partition(net.a, 0)
+            smp.set_partition(net.dead, 1)
+            smp.set_partition(net.b, 1)
     else:
         net = TwoHeads()
         if smp is not None:
@@ -70,6 +90,8 @@ def _loss(kind, model, x, y):
     if kind == "heads":
         a, d = model(x, scale=2.0)
         return ((a - y) ** 2).mean() + (d["aux"] ** 2).mean()
+    if kind == "unused":
+        return ((model(x, ignored=y) - y) ** 2).mean()
     return ((model(x) - y) ** 2).mean()
 
 
@@ -100,7 +122,7 @@ def _worker(rank, world, kind, auto):
     return {"losses": losses, "sd": sd, "parts": sorted(set(smp.state.module_manager.partition_info().values()))}
 
 
-@pytest.mark.parametrize("kind,auto", [("reuse", False), ("buffers", True), ("heads", False)])
+@pytest.mark.parametrize("kind,auto", [("reuse", False), ("buffers", True), ("heads", False), ("unused", False)])
 def test_pp2_toy_networks_match_single_process(kind, auto):
     res = run_distributed(_worker, 2, kind, auto)
     ref = _build(kind)
