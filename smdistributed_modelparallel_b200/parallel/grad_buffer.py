@@ -95,6 +95,46 @@ def _allreduce_sliced(flat: torch.Tensor, group, scale: float, bucket_elems: int
         flat.mul_(scale)
 
 
+class _HookBucket:
+    """What a DDP communication hook sees (the part of ``torch.distributed.GradBucket`` the stock hooks use)."""
+
+    def __init__(self, flat, index, last, params=()):
+        self._flat, self._index, self._last, self._params = flat, index, last, list(params)
+
+    def buffer(self):
+        return self._flat
+
+    def set_buffer(self, t):
+        self._flat = t
+
+    def index(self):
+        return self._index
+
+    def is_last(self):
+        return self._last
+
+    def parameters(self):
+        return self._params
+
+    def gradients(self):
+        return [self._flat]
+
+
+def _run_comm_hook(hook_state, hook, flat, bucket_elems):
+    """Hand ``flat`` to the user's hook bucket by bucket; the hook owns the reduction and the averaging over its
+    process group (as with torch DDP: reference torch/ddp_model.py:566-568 forwards hooks to the native reducer)."""
+    n = flat.numel()
+    starts = list(range(0, n, bucket_elems)) or [0]
+    for i, s0 in enumerate(starts):
+        piece = flat[s0:min(n, s0 + bucket_elems)]
+        fut = hook(hook_state, _HookBucket(piece, i, i == len(starts) - 1))
+        out = fut.wait() if hasattr(fut, "wait") else fut
+        if isinstance(out, (list, tuple)):
+            out = out[0]
+        if out.data_ptr() != piece.data_ptr():
+            piece.copy_(out.reshape(piece.shape))
+
+
 class GradReducer:
     """Data-parallel reduction of a GradBuffer (or of plain ``.grad`` tensors in fp32 training).
 
@@ -318,8 +358,10 @@ class GradReducer:
         scale = 1.0 / self.dp_size
         if self.grad_buffer is not None:
             if self.comm_hook is not None:
-                _allreduce_sliced(self.grad_buffer.region("scaled_batch"), self.rdp_group, scale, self.bucket_elems)
-                _allreduce_sliced(self.grad_buffer.region("default"), self.dp_group, scale, self.bucket_elems)
+                for region in ("scaled_batch", "default"):
+                    flat = self.grad_buffer.region(region)
+                    if flat.numel():
+                        _run_comm_hook(self.comm_hook[0], self.comm_hook[1], flat, self.bucket_elems)
                 return
             self._finish_overlapped()
             self.grad_buffer.buffer.mul_(scale)
@@ -334,7 +376,10 @@ class GradReducer:
                 by_dtype.setdefault(g.dtype, []).append(g)
             for dt, gs in by_dtype.items():
                 flat = torch.cat([g.reshape(-1) for g in gs])
-                _allreduce_sliced(flat, group, scale, self.bucket_elems)
+                if self.comm_hook is not None:
+                    _run_comm_hook(self.comm_hook[0], self.comm_hook[1], flat, self.bucket_elems)
+                else:
+                    _allreduce_sliced(flat, group, scale, self.bucket_elems)
                 off = 0
                 for g in gs:
                     g.copy_(flat[off:off + g.numel()].view_as(g))

@@ -13,7 +13,7 @@ CFG = dict(num_layers=2, num_attention_heads=4, attention_head_size=8, hidden_si
            post_layernorm=False, final_layernorm=True, use_normal_initialization=True)
 
 
-def _dp_worker(rank, world, shard, bf16):
+def _dp_worker(rank, world, shard, bf16, hook=None):
     import copy
 
     import smdistributed_modelparallel_b200 as smp
@@ -26,6 +26,19 @@ def _dp_worker(rank, world, shard, bf16):
     module = smp.nn.DistributedTransformerLMHead(**CFG)
     oracle = copy.deepcopy(module)
     model = smp.DistributedModel(module)
+    if hook == "allreduce":
+        from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+        model.register_comm_hook(smp.get_dp_process_group(), default_hooks.allreduce_hook)
+    elif hook == "custom":
+        calls = {"n": 0}
+
+        def my_hook(group, bucket):
+            calls["n"] += 1
+            t = bucket.buffer()
+            fut = torch.distributed.all_reduce(t, group=group, async_op=True).get_future()
+            return fut.then(lambda f: f.value()[0] / torch.distributed.get_world_size(group))
+
+        model.register_comm_hook(smp.get_dp_process_group(), my_hook)
     opt = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.01))
     oopt = torch.optim.AdamW(oracle.parameters(), lr=1e-2, weight_decay=0.01)
 
@@ -137,3 +150,13 @@ def test_tp2_loss_matches_dense(distribute_embedding, prescaled):
         for r, sl in zip(res, (slice(0, 2), slice(2, 4))):
             ol, _ = dense((ids_all[sl], None, None, None, ids_all[sl]))
             assert abs(r["loss"] - ol.item()) < 1e-4, (r["loss"], ol.item())
+
+
+@pytest.mark.parametrize("hook,bf16", [("allreduce", False), ("custom", True)])
+def test_dp2_with_comm_hook(hook, bf16):
+    """register_comm_hook: a DDP communication hook (torch's stock all-reduce hook, or a user future chain) replaces
+    the built-in reduction of every bucket; training still matches the dense model."""
+    res = run_distributed(_dp_worker, 2, False, bf16, hook)
+    for r in res:
+        assert r["worst"] < (5e-2 if bf16 else 4e-3), r
+        assert r["stats"]["overlapped_elems"] == 0          # the hook path does not use the built-in overlap
