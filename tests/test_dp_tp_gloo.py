@@ -160,3 +160,42 @@ def test_dp2_with_comm_hook(hook, bf16):
     for r in res:
         assert r["worst"] < (5e-2 if bf16 else 4e-3), r
         assert r["stats"]["overlapped_elems"] == 0          # the hook path does not use the built-in overlap
+
+
+def _accum_worker(rank, world):
+    import copy
+
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"ddp": True, "microbatches": 2, "ddp_dist_backend": "gloo"})
+    torch.manual_seed(3)
+    module = smp.nn.DistributedTransformerLMHead(**CFG)
+    oracle = copy.deepcopy(module)
+    model = smp.DistributedModel(module, backward_passes_per_step=2)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.5))
+    oopt = torch.optim.SGD(oracle.parameters(), lr=0.5)
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    torch.manual_seed(5)
+    all_ids = torch.randint(0, CFG["vocab_size"], (2, 4 * world, 16))
+    opt.zero_grad()
+    oopt.zero_grad()
+    for k in range(2):                                   # two @smp.step calls, gradients reduced only after the second
+        train_step(model, all_ids[k, rank * 4:(rank + 1) * 4])
+        ol, _ = oracle((all_ids[k], None, None, None, all_ids[k]))
+        ol.backward()
+    opt.step()
+    oopt.step()
+    return max((a.float() - b).abs().max().item() for a, b in zip(model.module.parameters(), oracle.parameters()))
+
+
+def test_backward_passes_per_step_accumulates_then_reduces():
+    """backward_passes_per_step=2: the first call only accumulates locally, the second triggers the data-parallel
+    reduction; the update equals the dense model's with both batches' gradients summed."""
+    res = run_distributed(_accum_worker, 2)
+    assert max(res) < 2e-5, res
