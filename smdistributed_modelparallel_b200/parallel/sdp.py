@@ -116,7 +116,15 @@ class ShardedDataParallelEngine:
         self.shard_rank = core.rank() % self.degree
         self.world = core.size()
         self.threshold = int(z.get("stage3_param_persistence_threshold", cfg.sdp_param_persistence_threshold))
-        self.unit_cap = int(os.environ.get("SMP_SDP_UNIT_ELEMENTS", z.get("stage3_prefetch_bucket_size", 5e8)))
+        # a unit is both the prefetch granule and the reduce-scatter granule, so it honours the smaller of the
+        # two bucket knobs (sdp_reduce_bucket_size / stage3_prefetch_bucket_size, in elements)
+        self.unit_cap = int(os.environ.get("SMP_SDP_UNIT_ELEMENTS",
+                                           min(float(z.get("stage3_prefetch_bucket_size", 5e8)),
+                                               float(z.get("reduce_bucket_size", cfg.sdp_reduce_bucket_size)))))
+        # sdp_hierarchical_allgather (two-level gather for shard groups spanning nodes) has nothing to do inside one
+        # NVSwitch domain, where every peer is one hop away; shard groups across nodes fall back to NCCL, which
+        # picks its own hierarchy
+        self.hierarchical = bool(z.get("zero2d_hierarchical_allgather", cfg.sdp_hierarchical_allgather))
         self.max_live = int(z.get("stage3_max_live_parameters", cfg.sdp_max_live_parameters))
         self.clip = float(cfg.zero2d_config_dict().get("gradient_clipping", cfg.sdp_gradient_clipping))
         self.device = state.device
