@@ -118,3 +118,43 @@ def test_unsupported_config_falls_back():
     model = smp.DistributedModel(hf)
     # the LM-head mapping declines this config; the per-layer / Linear / Embedding mappings may still apply
     assert type(model.module).__name__ != "DistributedTransformerLMHead"
+
+
+def test_vit_encoder_hooks_registered_by_hand():
+    """The ViT hooks ship unregistered (as in the reference); registered through smp.tp_register_with_module they
+    replace ViTEncoder and reproduce the HuggingFace output from the original checkpoint."""
+    from transformers import ViTConfig, ViTModel
+    from transformers.models.vit.modeling_vit import ViTEncoder
+
+    from smdistributed_modelparallel_b200.nn.huggingface import vit_t5 as V
+
+    smp.reset()
+    smp.init({"microbatches": 1})
+    tr = V.vit_translator()
+    smp.tp_register_with_module(ViTEncoder, smp.nn.DistributedTransformer, V.vit_encoder_init_hook,
+                                V.vit_encoder_forward_hook, V.vit_encoder_return_hook, (tr.smp_to_hf, tr.hf_to_smp))
+    torch.manual_seed(0)
+    cfg = ViTConfig(hidden_size=32, num_hidden_layers=2, num_attention_heads=4, intermediate_size=64, image_size=16,
+                    patch_size=4, hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    hf = ViTModel(cfg).eval()
+    sd = {k: v.clone() for k, v in hf.state_dict().items()}
+    x = torch.randn(2, 3, 16, 16)
+    with torch.no_grad():
+        ref = hf(pixel_values=x).last_hidden_state
+    with smp.tensor_parallelism(enabled=True):
+        hf2 = ViTModel(cfg)
+    model = smp.DistributedModel(hf2)
+    assert type(model.module.encoder).__name__ == "DistributedTransformer"
+    model.load_state_dict(sd)
+    model.eval()
+
+    @smp.step
+    def fwd(model, x):
+        return model(pixel_values=x).last_hidden_state
+
+    with torch.no_grad():
+        out = fwd(model, x).concat()
+    assert (out - ref).abs().max().item() < 1e-5
+    back = tr.smp_to_hf(model.state_dict())
+    for k, v in sd.items():
+        assert k in back and torch.equal(back[k], v), k
