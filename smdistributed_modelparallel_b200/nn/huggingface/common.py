@@ -124,8 +124,16 @@ def strip_prefix(sd, prefix):
 
 
 def check_unsupported(name, exc, **kwargs):
-    bad = [k for k, v in kwargs.items() if v is not None and v is not False and not (torch.is_tensor(v) and False)]
-    bad = [k for k in bad if not (isinstance(kwargs[k], (list, tuple)) and len(kwargs[k]) == 0)]
+    """Raise ``exc`` when a forward argument the distributed replacement cannot honour is actually used
+    (None, False and empty sequences count as unused)."""
+    def used(v):
+        if v is None or v is False:
+            return False
+        if isinstance(v, (list, tuple)) and len(v) == 0:
+            return False
+        return True
+
+    bad = [k for k, v in kwargs.items() if used(v)]
     if bad:
         raise exc(f"arguments {bad} of HuggingFace {name}.forward are not supported by the tensor-parallel replacement")
 
