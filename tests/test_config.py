@@ -78,3 +78,19 @@ def test_get_config_dict_round_trip():
     assert d["microbatches"] == 8 and d["pipeline_parallel_degree"] == 2
     c2 = ModelParallelConfig({k: v for k, v in d.items() if k in ("microbatches", "pipeline_parallel_degree")})
     assert c2.get_config_dict()["microbatches"] == 8
+
+
+def test_sagemaker_env_overrides_the_dict(monkeypatch):
+    monkeypatch.setenv("SM_HP_MP_PARAMETERS", '{"microbatches": 4, "pipeline": "simple"}')
+    c = ModelParallelConfig({"microbatches": 2, "pipeline_parallel_degree": 2})
+    # active_microbatches defaults to pipeline_parallel_degree + 2 = 4 = microbatches, so "simple" is kept
+    assert c.microbatches == 4 and c.pipeline == "simple" and c.pipeline_parallel_degree == 2
+    assert c.active_microbatches == 4
+
+
+def test_alias_conflict_and_formula_defaults():
+    with pytest.raises(SMPInvalidArgumentError):
+        ModelParallelConfig({"partitions": 2, "pipeline_parallel_degree": 4})
+    # active_microbatches defaults to microbatches; a different value forces the interleaved schedule
+    c = ModelParallelConfig({"pipeline_parallel_degree": 2, "microbatches": 8, "active_microbatches": 3, "pipeline": "simple"})
+    assert c.active_microbatches == 3 and c.pipeline == "interleaved"
