@@ -117,7 +117,7 @@ def _pp_tp_worker(rank, world, window, prescaled=False):
     return {"losses": losses, "full": full, "tp_rank": smp.tp_rank(), "pp_rank": smp.pp_rank(), "rank": rank}
 
 
-@pytest.mark.parametrize("window,prescaled", [(2, False), (4, False), (4, True)])
+@pytest.mark.parametrize("window,prescaled", [(2, False), (4, True)])
 def test_pp2_tp2_tracks_dense(window, prescaled):
     """Several optimizer steps must track the dense model (built here, tp=1) trained on the union of the
     tensor-parallel ranks' batches - every tp rank brings its own sequences."""
