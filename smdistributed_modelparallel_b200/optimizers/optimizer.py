@@ -189,7 +189,9 @@ class DistributedOptimizer:
             "dynamic_loss_scale": b.dynamic_loss_scale,
             "overflow": b.overflow,
             "first_closure_call_this_step": b.first_closure_call_this_step,
-            "fp32_from_fp16": [[m.detach().cpu() for m in grp] for grp in b.fp32_from_fp16_groups],
+            # under optimizer-state sharding the masters live in the shard slices (saved with the optimizer state)
+            "fp32_from_fp16": [] if self._opt_shard is not None
+            else [[m.detach().cpu() for m in grp] for grp in b.fp32_from_fp16_groups],
         }
 
     def load_optimizer_checkpoint_state(self, sd):
@@ -215,10 +217,13 @@ class DistributedOptimizer:
             b.dynamic_loss_scale = fp16["dynamic_loss_scale"]
             b.overflow = fp16["overflow"]
             b.first_closure_call_this_step = fp16["first_closure_call_this_step"]
-            for cur, saved in zip(b.fp32_from_fp16_groups, fp16["fp32_from_fp16"]):
-                for c, s in zip(cur, saved):
-                    c.data.copy_(s.to(c.device))
-            b.copy_master_to_model()
+            if self._opt_shard is None:
+                for cur, saved in zip(b.fp32_from_fp16_groups, fp16["fp32_from_fp16"]):
+                    for c, s in zip(cur, saved):
+                        c.data.copy_(s.to(c.device))
+                b.copy_master_to_model()
+            # with optimizer-state sharding the fp32 masters are the per-rank slices restored by load_shard_info;
+            # the wrapper's own (unused) master copies must not overwrite the parameters
 
     def load_optimizer_checkpoint(self, path, tag=None, partial=True, load_sharded_optimizer_state=True):
         from ..checkpoint import load_optimizer_from_checkpoint

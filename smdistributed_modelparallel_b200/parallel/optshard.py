@@ -46,6 +46,10 @@ class OptimizerStateSharding:
             for group, halfs, fulls in zip(optimizer.param_groups, bit16.fp16_groups, bit16.fp32_from_fp32_groups):
                 group["params"] = list(halfs) + list(fulls)
             optimizer.state.clear()
+            # ... and drop them: a full fp32 copy per rank is exactly what state sharding is meant to avoid
+            bit16.fp32_from_fp16_groups = [[] for _ in bit16.fp32_from_fp16_groups]
+            bit16._master_of.clear()
+            bit16._half_of.clear()
         params = []
         group_index = {}
         for gi, group in enumerate(optimizer.param_groups):

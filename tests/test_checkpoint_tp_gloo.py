@@ -85,3 +85,55 @@ def test_tp2_checkpoints():
     for k, v in sd.items():
         if k in res[0]["sd3"]:
             assert torch.equal(res[0]["sd3"][k], v), k
+
+
+def _optshard_worker(rank, world, ckpt_dir):
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"ddp": True, "microbatches": 1, "shard_optimizer_state": True, "bf16": True, "ddp_dist_backend": "gloo"})
+
+    def build(seed):
+        torch.manual_seed(seed)
+        with smp.model_creation(dtype=torch.bfloat16):
+            module = smp.nn.DistributedTransformerLMHead(**CFG)
+        model = smp.DistributedModel(module)
+        opt = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2))
+        return model, opt
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    def run(model, opt, n, seed):
+        g = torch.Generator().manual_seed(seed + rank)
+        out = []
+        for _ in range(n):
+            ids = torch.randint(0, CFG["vocab_size"], (2, 16), generator=g)
+            opt.zero_grad()
+            out.append(train_step(model, ids).reduce_mean().item())
+            opt.step()
+        return out
+
+    model, opt = build(1)
+    run(model, opt, 2, 10)
+    smp.save_checkpoint(ckpt_dir, tag="s", partial=True, model=model, optimizer=opt)
+    want = run(model, opt, 2, 20)
+    files = sorted(os.listdir(os.path.join(ckpt_dir, "s_partial")))
+    smp.reset()
+    model2, opt2 = build(99)
+    smp.resume_from_checkpoint(ckpt_dir, tag="s", partial=True)
+    got = run(model2, opt2, 2, 20)
+    return {"want": want, "got": got, "files": files}
+
+
+def test_optimizer_state_sharding_checkpoint():
+    """shard_optimizer_state: every data-parallel rank writes its own optimizer / 16-bit master slice
+    (``optimizer_states_{pp}_{tp}_{rdp}.pt``, the v3 naming) and training continues exactly after a resume."""
+    with tempfile.TemporaryDirectory() as d:
+        res = run_distributed(_optshard_worker, 2, d, timeout=300)
+    for r in res:
+        assert all(abs(a - b) < 1e-6 for a, b in zip(r["want"], r["got"])), (r["want"], r["got"])
+    files = set(res[0]["files"])
+    assert {"optimizer_states_0_0_0.pt", "optimizer_states_0_0_1.pt", "model_0_0.pt"} <= files, files
