@@ -141,3 +141,45 @@ def test_save_load_partial_names():
         assert smp.load(os.path.join(d, "obj"), partial=True) == {"a": 1}
         smp.save({"b": 2}, os.path.join(d, "whole.pt"), partial=False)
         assert smp.load(os.path.join(d, "whole.pt"), partial=False) == {"b": 2}
+
+
+def test_bf16_masters_survive_a_resume():
+    """16-bit training keeps fp32 master weights in the optimizer wrapper; a partial checkpoint stores them
+    (fp16_states) and the run continues bit-for-bit after a resume."""
+    with tempfile.TemporaryDirectory() as d:
+        def build(seed):
+            smp.reset()
+            smp.init({"microbatches": 2, "bf16": True})
+            torch.manual_seed(seed)
+            with smp.model_creation(dtype=torch.bfloat16):
+                net = nn.Sequential(nn.Linear(8, 16), nn.Tanh(), nn.Linear(16, 4))
+            model = smp.DistributedModel(net)
+            opt = smp.DistributedOptimizer(torch.optim.Adam(model.parameters(), lr=1e-2))
+
+            @smp.step
+            def train_step(model, x, y):
+                loss = ((model(x).float() - y) ** 2).mean()
+                model.backward(loss)
+                return loss
+
+            return model, opt, train_step
+
+        def run(model, opt, step, n, seed):
+            g = torch.Generator().manual_seed(seed)
+            out = []
+            for _ in range(n):
+                x, y = torch.randn(4, 8, generator=g).bfloat16(), torch.randn(4, 4, generator=g)
+                opt.zero_grad()
+                out.append(step(model, x, y).reduce_mean().item())
+                opt.step()
+            return out
+
+        model, opt, step = build(0)
+        run(model, opt, step, 3, 1)
+        smp.save_checkpoint(d, tag="b", model=model, optimizer=opt)
+        assert "fp16_states_0_0.pt" in os.listdir(os.path.join(d, "b_partial"))
+        want = run(model, opt, step, 3, 2)
+        model2, opt2, step2 = build(42)
+        smp.resume_from_checkpoint(d, tag="b")
+        got = run(model2, opt2, step2, 3, 2)
+        assert want == got, (want, got)

@@ -185,3 +185,69 @@ def test_pp4_matches_dense():
         assert r["n_local"] > 0
     layers = res[0]["layers"]
     assert sorted(set(layers)) == [0, 1, 2, 3] and layers == sorted(layers), layers
+
+
+def _pp_dp_worker(rank, world):
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": True, "bf16": True, "ddp_dist_backend": "gloo"})
+    torch.manual_seed(7)
+    with smp.model_creation(dtype=torch.bfloat16):
+        module = smp.nn.DistributedTransformerLMHead(**CFG)
+    smp.set_activation_checkpointing(module.transformer.seq_layers, pack_args_as_tuple=True, strategy="group_2")
+    model = smp.DistributedModel(module)
+    opt = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2))
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    @smp.step
+    def eval_step(model, ids):
+        return model((ids, None, None, None, ids))[0]
+
+    torch.manual_seed(11)
+    all_ids = torch.randint(0, CFG["vocab_size"], (4, 8, 16))
+    with torch.no_grad():
+        eval_step(model, all_ids[0, :4])
+    full = {k: v.float().clone() for k, v in model.state_dict().items()}
+    losses = []
+    for it in range(4):
+        ids = all_ids[it, smp.dp_rank() * 4:(smp.dp_rank() + 1) * 4]
+        opt.zero_grad()
+        losses.append(train_step(model, ids).reduce_mean().item())
+        opt.step()
+    after = {k: v.float().clone() for k, v in model.state_dict().items()}
+    return {"losses": losses, "full": full, "after": after, "pp_rank": smp.pp_rank(), "dp_rank": smp.dp_rank(), "rank": rank}
+
+
+def test_pp2_dp2_bf16_with_activation_checkpointing():
+    """Two pipeline stages x two data-parallel replicas, bf16 with fp32 masters, group_2 activation checkpointing:
+    parameters after four AdamW steps track the dense fp32 model trained on both replicas' batches."""
+    res = run_distributed(_pp_dp_worker, 4, timeout=420)
+    import smdistributed_modelparallel_b200  # noqa: F401
+    from smdistributed_modelparallel_b200.nn.transformer import DistributedTransformerLMHead
+
+    dense = DistributedTransformerLMHead(**CFG)
+    r0 = next(r for r in res if r["rank"] == 0)
+    dense.load_state_dict(r0["full"], strict=False)
+    oopt = torch.optim.AdamW(dense.parameters(), lr=1e-2)
+    torch.manual_seed(11)
+    all_ids = torch.randint(0, CFG["vocab_size"], (4, 8, 16))
+    for it in range(4):
+        oopt.zero_grad()
+        ol, _ = dense((all_ids[it], None, None, None, all_ids[it]))
+        ol.backward()
+        oopt.step()
+        leaders = [r for r in res if r["pp_rank"] == 0]
+        mean = sum(r["losses"][it] for r in leaders) / len(leaders)
+        assert abs(mean - ol.item()) < 5e-2, (it, mean, ol.item())
+    dsd = dense.state_dict()
+    worst = max((r0["after"][k] - dsd[k]).abs().max().item() for k in dsd if k in r0["after"])
+    assert worst < 5e-2, worst
+    # replicas hold identical parameters
+    other = next(r for r in res if r["pp_rank"] == 0 and r["dp_rank"] == 1)
+    for k, v in r0["after"].items():
+        assert torch.equal(v, other["after"][k]), k
