@@ -39,6 +39,10 @@ class DistributedOptimizer:
         self._dynamic_loss_scale = dynamic_loss_scale
         self._dynamic_loss_args = dynamic_loss_args
         self.redefined_params = False
+        # delayed parameter initialisation replaces meta parameters by materialised ones after the partition is
+        # known (pp > 1: at the first step, i.e. after this wrapper exists): remember every parameter's name so the
+        # inner optimizer can be pointed at the real tensors then
+        self._names_at_creation = {id(p): n for n, p in self.model.module.named_parameters(remove_duplicate=False)}
         state.optimizer = self
         self.model._call_after_partitioning(self._after_partition)
         if state.loaded_optimizer_state is not None:
@@ -52,8 +56,22 @@ class DistributedOptimizer:
         self._post_partition_done = True
         cfg = state.cfg
         local = {id(p) for p in model.local_parameters()}
+        by_name = dict(model.module.named_parameters(remove_duplicate=False))
         for group in self.optimizer.param_groups:
-            group["params"] = [p for p in group["params"] if id(p) in local]
+            kept, seen = [], set()
+            for p in group["params"]:
+                q = p
+                if id(p) not in local:                       # stale (meta) object: look the parameter up by name
+                    q = by_name.get(self._names_at_creation.get(id(p)))
+                    if q is None or id(q) not in local:
+                        continue
+                    if p in self.optimizer.state:
+                        self.optimizer.state[q] = self.optimizer.state.pop(p)
+                    self.redefined_params = True
+                if id(q) not in seen:
+                    seen.add(id(q))
+                    kept.append(q)
+            group["params"] = kept
         self._build_name_maps()
         if model.sdp_engine is not None:
             model.sdp_engine.attach_optimizer(self.optimizer, clip=cfg.sdp_gradient_clipping,

@@ -251,3 +251,47 @@ def test_pp2_dp2_bf16_with_activation_checkpointing():
     other = next(r for r in res if r["pp_rank"] == 0 and r["dp_rank"] == 1)
     for k, v in r0["after"].items():
         assert torch.equal(v, other["after"][k]), k
+
+
+def _delayed_worker(rank, world):
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": False, "delayed_parameter_initialization": True})
+    with smp.model_creation():
+        module = smp.nn.DistributedTransformerLMHead(**CFG)
+    assert all(p.is_meta for p in module.parameters()), "nothing may be materialised before partitioning"
+    model = smp.DistributedModel(module)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    torch.manual_seed(11)
+    ids = torch.randint(0, CFG["vocab_size"], (8, 16))
+    losses = []
+    for _ in range(3):
+        opt.zero_grad()
+        losses.append(train_step(model, ids).reduce_mean().item())
+        opt.step()
+    local = list(model.local_parameters())
+    everything = list(model.module.parameters())
+    return {"losses": losses, "local_elems": sum(p.numel() for p in local),
+            "held_elems": sum(p.numel() for p in everything if not p.is_meta),
+            "meta_left": sum(1 for p in local if p.is_meta)}
+
+
+def test_delayed_parameter_initialisation_under_pp():
+    """delayed_parameter_initialization: the model is built on the meta device; after partitioning each pipeline rank
+    materialises (and initialises) only the parameters it owns, and training runs."""
+    res = run_distributed(_delayed_worker, 2, timeout=300)
+    total = 0
+    for r in res:
+        assert r["meta_left"] == 0
+        assert r["held_elems"] == r["local_elems"], r          # nothing beyond the local partition holds storage
+        assert all(l == l for l in r["losses"]) and r["losses"][-1] < r["losses"][0]
+        assert r["losses"][0] < 4.6, r["losses"]      # ~ln(64): the constructor's initialisers were replayed
+        total += r["local_elems"]
+    assert res[0]["local_elems"] > 0 and res[1]["local_elems"] > 0 and total > 0

@@ -184,3 +184,39 @@ def test_amp_grad_scaler_single_process():
     scaler.update()
     assert torch.allclose(w.detach(), torch.full((3,), 0.8))
     assert math.isclose(scaler.get_scale(), 1.0)
+
+
+def test_fp16_dynamic_loss_scale_skips_overflowing_steps():
+    """fp16 with dynamic loss scaling: a step whose scaled gradients overflow is skipped (parameters and optimizer
+    state untouched, scale halved); once the scale fits, training proceeds."""
+    import torch.nn as nn
+
+    smp.reset()
+    smp.init({"microbatches": 1, "fp16": True})
+    torch.manual_seed(0)
+    with smp.model_creation(dtype=torch.float16):
+        net = nn.Sequential(nn.Linear(8, 16), nn.Tanh(), nn.Linear(16, 4))
+    model = smp.DistributedModel(net)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1), dynamic_loss_scale=True,
+                                   dynamic_loss_args={"init_scale": 2.0 ** 30, "scale_window": 1000})
+
+    @smp.step
+    def train_step(model, x, y):
+        loss = ((model(x).float() - y) ** 2).mean()
+        model.backward(loss)
+        return loss
+
+    x, y = torch.randn(4, 8).half(), torch.randn(4, 4)
+    before = [p.detach().clone() for p in model.module.parameters()]
+    scales, changed = [], []
+    for _ in range(24):
+        opt.zero_grad()
+        train_step(model, x, y)
+        opt.step()
+        scales.append(float(opt.loss_scale))
+        changed.append(any(not torch.equal(a, b.detach()) for a, b in zip(before, model.module.parameters())))
+    assert scales[0] == 2.0 ** 29 and not changed[0]          # the first step overflowed and was skipped
+    first_ok = changed.index(True)
+    assert first_ok > 0 and scales[first_ok] == scales[first_ok - 1]   # the scale stops shrinking once a step fits
+    assert all(s == scales[-1] for s in scales[first_ok:])
+    assert all(torch.isfinite(p).all() for p in model.module.parameters())
