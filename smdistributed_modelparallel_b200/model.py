@@ -270,28 +270,28 @@ class DistributedModel(nn.Module):
             self.sdp_engine._sync_step = sync
         ran_backward = {"v": False}
         self._ran_backward = ran_backward
-        try:
-            yield
-        finally:
-            if torch.is_grad_enabled() and self._partitioned:
-                opt = state.optimizer
-                shard = getattr(opt, "_opt_shard", None) if opt is not None else None
-                if self.sdp_engine is not None:
-                    self.sdp_engine.reduce_epilogue(sync)
-                elif shard is not None:
-                    if sync:
-                        shard.reduce_gradients()
-                        shard.check_overflow()
-                else:
-                    if self.reducer is not None and sync:
-                        self.reducer.synchronize()
-                    if opt is not None and sync and hasattr(opt, "update_master_grads"):
-                        opt.update_master_grads()
-                for hook in list(self._post_step_hooks.values()):
-                    hook(self, opt)
-            self._num_steps += 1
-            if state.core.pp_size() > 1:
-                state.comm.pp_barrier()
+        # An exception inside the step propagates untouched: the reductions and the barrier below are
+        # collectives, and entering them on the ranks that failed would turn the error into a hang.
+        yield
+        if torch.is_grad_enabled() and self._partitioned:
+            opt = state.optimizer
+            shard = getattr(opt, "_opt_shard", None) if opt is not None else None
+            if self.sdp_engine is not None:
+                self.sdp_engine.reduce_epilogue(sync)
+            elif shard is not None:
+                if sync:
+                    shard.reduce_gradients()
+                    shard.check_overflow()
+            else:
+                if self.reducer is not None and sync:
+                    self.reducer.synchronize()
+                if opt is not None and sync and hasattr(opt, "update_master_grads"):
+                    opt.update_master_grads()
+            for hook in list(self._post_step_hooks.values()):
+                hook(self, opt)
+        self._num_steps += 1
+        if state.core.pp_size() > 1:
+            state.comm.pp_barrier()
 
     def zero_grad_buffer(self):
         if self.grad_buffer is not None:
@@ -391,10 +391,12 @@ class DistributedModel(nn.Module):
         return self
 
     # ------------------------------------------------------------------ hooks
-    def register_post_partition_hook(self, hook) -> RemovableHandle:
+    def register_post_partition_hook(self, hook, prepend=False) -> RemovableHandle:
         """hook(model, optimizer) runs right after partitioning (immediately if already partitioned)."""
         handle = RemovableHandle(self._post_partition_hooks)
         self._post_partition_hooks[handle.id] = hook
+        if prepend:
+            self._post_partition_hooks.move_to_end(handle.id, last=False)
         if self._partitioned:
             hook(self, state.optimizer)
         return handle
@@ -472,7 +474,10 @@ class DistributedModel(nn.Module):
             info = info if isinstance(info, dict) else None
             if same_partition_load and info and info.get("partition_info"):
                 self.load_saved_partition(info["partition_info"])
-            self.register_post_partition_hook(_do)
+            # a deferred model load runs before the optimizer wrapper's own post-partition work: the wrapper first
+            # copies model -> fp32 masters, then a pending optimizer checkpoint restores the exact masters (the same
+            # order as loading into an already partitioned model)
+            self.register_post_partition_hook(_do, prepend=True)
             return None
         return _do(self)
 

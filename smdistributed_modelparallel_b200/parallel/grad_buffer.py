@@ -250,6 +250,9 @@ class GradReducer:
         self._contrib = {}            # param id -> accumulations per microbatch, when more than one
         for p in order:
             self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
+        # under pipeline parallelism the model is partitioned inside the first step, after that step's
+        # prepare_for_backward has already run: arm the counter for the step in progress
+        self.prepare_for_backward()
         return nb
 
     def prepare_for_backward(self):

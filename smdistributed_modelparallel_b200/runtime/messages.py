@@ -87,9 +87,11 @@ class BackwardResult:
 
 @dataclass
 class StepDone:
-    """Leader -> followers: every microbatch finished; carries the step function's (detached) outputs."""
+    """Leader -> followers: every microbatch finished; carries the step function's (detached) outputs, or
+    the text of the exception that ended the step on the leader."""
     step: int
     outputs: Any = None
+    error: Any = None
 
 
 @dataclass

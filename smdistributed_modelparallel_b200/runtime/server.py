@@ -636,6 +636,13 @@ class ExecutionServer:
                     _Scheduler(self, [(mb, "fwd") for mb in range(num_mb)], window).run()
                     _Scheduler(self, [(mb, "bwd") for mb in range(num_mb) if mb in self.deferred_bwd], window).run()
                 outputs = self._step_ctx["outputs"]
+            except BaseException as exc:
+                # the other stages are waiting for this step to end: tell them it ended badly, so that the
+                # job fails everywhere instead of hanging on the ranks that saw nothing wrong
+                for r in group:
+                    if r != self.me:
+                        self.comm.server_send(StepDone(self._step, None, f"{type(exc).__name__}: {exc}"), r)
+                raise
             finally:
                 self._step_ctx = None
             wire = map_structure(lambda x: x.cpu() if torch.is_tensor(x) else x, outputs)
@@ -645,6 +652,8 @@ class ExecutionServer:
         else:
             while self._done_msg is None:
                 self._pump_one(50)
+            if self._done_msg.error is not None:
+                raise SMPRuntimeError(f"the step failed on pipeline rank 0: {self._done_msg.error}")
             dev = st.device
             outputs = map_structure(lambda x: x.to(dev) if torch.is_tensor(x) else x, self._done_msg.outputs)
         self.p2p.drain()

@@ -295,3 +295,79 @@ def test_delayed_parameter_initialisation_under_pp():
         assert r["losses"][0] < 4.6, r["losses"]      # ~ln(64): the constructor's initialisers were replayed
         total += r["local_elems"]
     assert res[0]["local_elems"] > 0 and res[1]["local_elems"] > 0 and total > 0
+
+
+def _pp_optshard_worker(rank, world):
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": True, "fp16": True, "shard_optimizer_state": True,
+              "ddp_dist_backend": "gloo"})
+    torch.manual_seed(7)
+    with smp.model_creation(dtype=torch.float16):
+        module = smp.nn.DistributedTransformerLMHead(**CFG)
+    model = smp.DistributedModel(module)
+    opt = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=5e-3), dynamic_loss_scale=True,
+                                   dynamic_loss_args={"init_scale": 2.0 ** 12, "scale_window": 3})
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    torch.manual_seed(100 + smp.dp_rank())
+    ids = torch.randint(0, CFG["vocab_size"], (4, 16))
+    losses, scales = [], []
+    for _ in range(10):
+        opt.zero_grad()
+        out = train_step(model, ids)
+        opt.step()
+        losses.append(out.reduce_mean().item())
+        scales.append(float(opt.loss_scale))
+    sd = {k: v.float().clone() for k, v in model.state_dict().items()}
+    return {"losses": losses, "scales": scales, "sd": sd, "pp_rank": smp.pp_rank(), "dp_rank": smp.dp_rank()}
+
+
+def test_pp2_dp2_fp16_dynamic_scale_with_optimizer_state_sharding():
+    """Pipeline x data parallel with fp16 dynamic loss scaling and optimizer-state sharding: overflow decisions are
+    shared by every rank (same scale history), the loss falls, replicas stay identical."""
+    res = run_distributed(_pp_optshard_worker, 4, timeout=420)
+    for r in res:
+        assert r["scales"] == res[0]["scales"], (r["scales"], res[0]["scales"])
+        if r["pp_rank"] == 0:
+            assert all(l == l for l in r["losses"]) and r["losses"][-1] < r["losses"][0] - 0.2, r["losses"]
+    for r in res[1:]:
+        for k, v in res[0]["sd"].items():
+            assert torch.equal(v, r["sd"][k]), k
+
+
+def _failing_step_worker(rank, world):
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": False})
+    torch.manual_seed(7)
+    model = smp.DistributedModel(smp.nn.DistributedTransformerLMHead(**CFG))
+
+    @smp.step
+    def bad_step(model, ids, fail):
+        loss, _ = model((ids, None, None, None, ids))
+        if fail:
+            raise ValueError("deliberate failure in the step function")
+        model.backward(loss)
+        return loss
+
+    ids = torch.randint(0, CFG["vocab_size"], (4, 16), generator=torch.Generator().manual_seed(3))
+    ok = bad_step(model, ids, False).reduce_mean().item()
+    try:
+        bad_step(model, ids, True)
+    except Exception as e:   # noqa: BLE001
+        return {"ok": ok, "error": f"{type(e).__name__}: {e}"}
+    return {"ok": ok, "error": None}
+
+
+def test_step_failure_reaches_every_pipeline_rank():
+    """An exception raised by the step function on the leader ends the step on the other stage too (it is told
+    why), instead of leaving it waiting for messages that will never come."""
+    res = run_distributed(_failing_step_worker, 2, timeout=180)
+    assert "deliberate failure" in res[0]["error"] and res[0]["error"].startswith("ValueError")
+    assert "deliberate failure" in res[1]["error"], res[1]
