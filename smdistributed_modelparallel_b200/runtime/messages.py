@@ -58,6 +58,10 @@ class ForwardRequest:
     skeleton: Any                 # (args, kwargs) with TensorStubs
     grad_enabled: bool
     requester: int                # global rank
+    # fast mode: the chunks [(global rank, (first child, last child + 1))] still to run after this one; the
+    # output goes straight to the next of them and only the last one answers the requester
+    chain: tuple = ()
+    prev_hop: int | None = None   # the chain stage this request came from (None: from the requester)
 
 
 @dataclass

@@ -141,12 +141,13 @@ def test_pp2_tp2_tracks_dense(window, prescaled):
         assert abs(mean - ol.item()) < 3e-5, (it, mean, ol.item())
 
 
-def _pp4_worker(rank, world):
+def _pp4_worker(rank, world, fast_mode=False):
     import copy
 
     import smdistributed_modelparallel_b200 as smp
 
-    smp.init({"pipeline_parallel_degree": 4, "microbatches": 4, "ddp": False, "active_microbatches": 3})
+    smp.init({"pipeline_parallel_degree": 4, "microbatches": 4, "ddp": False, "active_microbatches": 3,
+              "fast_mode": fast_mode})
     torch.manual_seed(7)
     cfg = dict(CFG, num_layers=8)
     module = smp.nn.DistributedTransformerLMHead(**cfg)
@@ -172,19 +173,32 @@ def _pp4_worker(rank, world):
         worst = max(worst, (p.grad - ref[n]).abs().max().item())
         n_local += 1
     layers = [smp.state.module_manager.get_partition(l) for l in model.module.transformer.seq_layers]
-    return {"loss": loss, "oracle": ol.item(), "worst": worst, "n_local": n_local, "layers": layers}
+    opt.step()
+    loss2 = train_step(model, ids).reduce_mean().item()
+    return {"loss": loss, "oracle": ol.item(), "worst": worst, "n_local": n_local, "layers": layers,
+            "loss2": loss2, "hop_bytes": smp.state.module_manager.comm_volume_bytes}
 
 
-def test_pp4_matches_dense():
+@pytest.mark.parametrize("fast_mode", [False, True])
+def test_pp4_matches_dense(fast_mode):
     """Four pipeline stages (reference test/torch/mpi_4ps): the layer stack is cut into four contiguous chunks
-    served in sequence; loss and every local gradient match the dense model."""
-    res = run_distributed(_pp4_worker, 4, timeout=420)
+    served in sequence; loss and every local gradient match the dense model.  In fast mode the chunks hand
+    their outputs to one another directly (and the gradients walk back the same way), so the leader moves
+    far fewer bytes."""
+    res = run_distributed(_pp4_worker, 4, fast_mode, timeout=420)
     for r in res:
         assert abs(r["loss"] - r["oracle"]) < 1e-5, r
         assert r["worst"] < 1e-5, r
         assert r["n_local"] > 0
+        assert r["loss2"] < r["loss"]
     layers = res[0]["layers"]
     assert sorted(set(layers)) == [0, 1, 2, 3] and layers == sorted(layers), layers
+    test_pp4_matches_dense.leader_bytes[fast_mode] = res[0]["hop_bytes"]
+    if len(test_pp4_matches_dense.leader_bytes) == 2:
+        assert test_pp4_matches_dense.leader_bytes[True] < 0.6 * test_pp4_matches_dense.leader_bytes[False]
+
+
+test_pp4_matches_dense.leader_bytes = {}
 
 
 def _pp_dp_worker(rank, world):
