@@ -305,3 +305,66 @@ SMPC_API int smpc_device_count() {
   }
   return n;
 }
+
+// ---- in-library self-test (the reference ships native self-tests inside its library as well: test_d2d(),
+// from_blob_tensor_test(), test_rdma_p2p() - SURVEY 2.2 N1e).  Exercises the gradient counter, the bucket
+// planner and the pool metrics through the same C ABI the Python side uses.  Returns 0, or the number of the
+// first failed check with a description in `msg`.
+SMPC_API int smpc_selftest_runtime(char* msg, int cap) {
+  int check = 0;
+  auto bad = [&](const char* what) {
+    if (msg && cap > 0) snprintf(msg, (size_t)cap, "check %d failed: %s", check, what);
+    return check;
+  };
+#define SMPC_EXPECT(cond) do { ++check; if (!(cond)) return bad(#cond); } while (0)
+  // gradient counter: 3 parameters, 2 microbatches; parameter 2 is used twice per microbatch
+  void* g = smpc_gc_create(3, 2);
+  SMPC_EXPECT(g != nullptr);
+  const int ids[4] = {0, 1, 2, 2};
+  for (int mb = 0; mb < 2; ++mb) {
+    SMPC_EXPECT(smpc_gc_increment_expected(g, mb, ids, 4) == 0);
+    SMPC_EXPECT(smpc_gc_mark_fwd_done(g, mb) == 0);
+  }
+  SMPC_EXPECT(smpc_gc_expected(g, 1, 2) == 2 && smpc_gc_expected(g, 0, 0) == 1);
+  smpc_gc_set_microbatch(g, 0);
+  SMPC_EXPECT(smpc_gc_get_microbatch(g) == 0);
+  SMPC_EXPECT(smpc_gc_mark_grad_computed(g, 0) == 0);
+  SMPC_EXPECT(smpc_gc_mark_grad_computed(g, 0) == -2);      // more than announced
+  SMPC_EXPECT(smpc_gc_mark_grad_computed(g, 2) == 0 && smpc_gc_mark_grad_computed(g, 2) == 0);
+  SMPC_EXPECT(smpc_gc_is_ready(g, 0) == 0 && smpc_gc_mark_grad_computed(g, 7) == -1);
+  smpc_gc_set_microbatch(g, 1);
+  SMPC_EXPECT(smpc_gc_mark_grad_computed(g, 0) == 1);       // last contribution of the last microbatch
+  SMPC_EXPECT(smpc_gc_mark_grad_computed(g, 2) == 0 && smpc_gc_mark_grad_computed(g, 2) == 1);
+  SMPC_EXPECT(smpc_gc_is_ready(g, 2) == 1 && smpc_gc_is_ready(g, 1) == 0);
+  SMPC_EXPECT(smpc_gc_seen(g, 1, 2) == 2);
+  int totals[3] = {0, 0, 0};
+  smpc_gc_expected_totals(g, totals);
+  SMPC_EXPECT(totals[0] == 2 && totals[1] == 2 && totals[2] == 4);
+  smpc_gc_clear(g);
+  SMPC_EXPECT(smpc_gc_expected(g, 0, 0) == 0 && smpc_gc_seen(g, 1, 2) == 0);
+  smpc_gc_destroy(g);
+  // bucket planner: a small first bucket, a size cap, and a key change always starts a new bucket
+  const long long nbytes[6] = {600, 600, 3000, 3000, 100, 100};
+  const int keys[6] = {0, 0, 0, 0, 0, 1};
+  int bucket_of[6] = {-1, -1, -1, -1, -1, -1};
+  const int nb = smpc_plan_buckets(6, nbytes, keys, 1000, 5000, bucket_of);
+  SMPC_EXPECT(nb >= 3);
+  SMPC_EXPECT(bucket_of[0] == 0 && bucket_of[5] == nb - 1 && bucket_of[4] != bucket_of[5]);
+  for (int i = 1; i < 6; ++i) SMPC_EXPECT(bucket_of[i] >= bucket_of[i - 1]);
+  SMPC_EXPECT(bucket_of[2] != bucket_of[0]);                // the first bucket closes at first_cap
+  // pool metrics accumulate and reset
+  long long am[2];
+  smpc_get_and_reset_alloc_metrics(am);
+  smpc_pool_record(1 << 20, 2 << 20, 1);
+  smpc_pool_record(0, 4 << 20, 0);                       // a reservation that failed
+  smpc_pool_record(0, -(4 << 20), 1);
+  smpc_get_and_reset_alloc_metrics(am);
+  SMPC_EXPECT(am[0] == 1 && am[1] == 1);
+  smpc_get_and_reset_alloc_metrics(am);
+  SMPC_EXPECT(am[0] == 0 && am[1] == 0);
+  smpc_pool_record(-(1 << 20), -(2 << 20), 1);
+  smpc_get_and_reset_alloc_metrics(am);
+#undef SMPC_EXPECT
+  if (msg && cap > 0) snprintf(msg, (size_t)cap, "ok: %d checks", check);
+  return 0;
+}

@@ -57,6 +57,9 @@ void smpc_pool_record(long long delta_alloc, long long delta_reserved, int ok);
 int smpc_get_and_reset_memory_metrics(double* out4);
 int smpc_get_and_reset_alloc_metrics(long long* out2);
 int smpc_device_count(void);
+/* in-library self-test of the counter, the bucket planner and the metrics (the reference's library carries
+ * native self-tests too: test/backend/d2d_test.py:11, from_blob_tensor_test.py:11); 0 = ok */
+int smpc_selftest_runtime(char* msg, int cap);
 
 /* ---- symmetric (peer-addressable) memory over CUDA IPC (no counterpart among the reference's Python-visible
  *      entry points; replaces NCCL for tensor-parallel traffic: torch/nn/utils.py:701-821) */
@@ -66,6 +69,7 @@ int smpc_symm_open(const unsigned char* handle64, void** peer_ptr);
 int smpc_symm_close(void* peer_ptr);
 int smpc_symm_free(void* dev_ptr);
 int smpc_symm_can_access_peer(int peer_device);
+int smpc_symm_selftest(long long bytes);                                /* needs a GPU; 0 = ok */
 
 #ifdef __cplusplus
 }

@@ -65,7 +65,27 @@ _SIG = {
     "smpc_symm_close": ([P], I),
     "smpc_symm_free": ([P], I),
     "smpc_symm_can_access_peer": ([I], I),
+    "smpc_symm_selftest": ([L], I),
+    "smpc_selftest_runtime": ([ctypes.c_char_p, I], I),
 }
+
+
+def selftest(gpu: bool = False) -> str:
+    """Run the library's own self-tests (reference test/backend/d2d_test.py:11, from_blob_tensor_test.py:11 call
+    the same kind of in-library checks).  Returns the summary line; raises on a failed check."""
+    lib = load()
+    buf = ctypes.create_string_buffer(256)
+    rc = lib.smpc_selftest_runtime(buf, len(buf))
+    if rc != 0:
+        raise RuntimeError(f"native runtime self-test: {buf.value.decode()}")
+    msg = buf.value.decode()
+    if gpu:
+        rc = lib.smpc_symm_selftest(1 << 20)
+        if rc != 0:
+            raise RuntimeError(f"symmetric-memory self-test failed ({rc}): {lib.smpc_symm_last_error().decode()}")
+        msg += "; symmetric memory ok"
+    return msg
+
 _OPTIONAL: dict = {}
 
 

@@ -70,9 +70,12 @@ class PipelineP2P:
     """Tensor transport between pipeline ranks: one 2-rank group per ordered (src, dst) pair."""
 
     def __init__(self, state):
+        from .links import HandleManager, LinkManager
+
         self.state = state
         self.me = state.core.rank()
-        self._inflight = []
+        self.links = LinkManager(state.core.pp_rank())     # one link per transfer slot, recycled every step
+        self.handles = HandleManager()                     # keeps in-flight sends (and their tensors) alive
 
     def _wire(self, t):
         t = t.detach()
@@ -85,11 +88,12 @@ class PipelineP2P:
         nbytes = 0
         for t in tensors:
             w = self._wire(t)
+            n = w.numel() * w.element_size()
             work = dist.isend(w, dst=dst, group=group)
-            self._inflight.append((work, w))
-            nbytes += w.numel() * w.element_size()
+            self.handles.register_handle(work, self.handles.SEND, w, self.links.get_link(n))
+            nbytes += n
         self.state.module_manager.record_hop(nbytes)
-        self._reap()
+        self.handles.reap(self.handles.SEND)
 
     def recv(self, metas, src, device, defer=False):
         """metas: [(shape, dtype)] -> list of tensors.  The receives are posted now (posting order must follow
@@ -111,13 +115,12 @@ class PipelineP2P:
 
         return finish if defer else finish()
 
-    def _reap(self):
-        self._inflight = [(w, t) for (w, t) in self._inflight if not w.is_completed()]
-
     def drain(self):
-        for w, _ in self._inflight:
-            w.wait()
-        self._inflight = []
+        """End of step: every send has left; the links are free for the next step."""
+        for h in self.handles.handles():
+            self.handles.wait(h)
+            self.handles.clear_handle(h)
+        self.links.reset()
 
 
 _task_local = threading.local()

@@ -154,3 +154,57 @@ def test_peer_failure_aborts_blocking_receive():
     res = run_distributed(_failure_worker, 2, timeout=120)
     assert res[1] == "failed-on-purpose"
     assert res[0].startswith("aborted"), res[0]
+
+
+def test_in_library_selftest():
+    """The native library checks its own counter / planner / metrics through the C ABI."""
+    from smdistributed_modelparallel_b200.backend import native_core
+
+    msg = native_core.selftest()
+    assert msg.startswith("ok:"), msg
+    assert int(msg.split()[1]) >= 20
+
+
+def test_link_manager_reuses_slots_by_size():
+    """Link ids: smallest free link that fits, a fresh one otherwise, everything free again after reset; each
+    pipeline rank draws from its own id range (reference torch/links.py:21-84)."""
+    from smdistributed_modelparallel_b200.runtime.links import IDS_PER_RANK, HandleManager, LinkManager
+
+    lm = LinkManager(pp_rank=2)
+    a = lm.get_link(1000)
+    b = lm.get_link(1000)
+    c = lm.get_link(4000)
+    assert len({a, b, c}) == 3 and all(2 * IDS_PER_RANK < x < 3 * IDS_PER_RANK for x in (a, b, c))
+    assert lm.in_use() == 3
+    lm.reset()
+    assert lm.in_use() == 0 and lm.wasted_bytes() == 6000
+    # a smaller request takes the smallest link that is large enough
+    assert lm.get_link(900) in (a, b)
+    assert lm.get_link(900) in (a, b)
+    assert lm.get_link(900) == c               # both 1000-byte links are busy: the 4000-byte one fits
+    d = lm.get_link(900)                       # nothing free: a new link of exactly that size
+    assert d not in (a, b, c) and lm.link_size(d) == 900
+    assert lm.stats[c] == [2, 4900]
+    lm.reset()
+    assert LinkManager(pp_rank=0).get_link(8) < IDS_PER_RANK
+
+    class _Work:
+        def __init__(self, done):
+            self.done = done
+
+        def is_completed(self):
+            return self.done
+
+        def wait(self):
+            self.done = True
+
+    hm = HandleManager()
+    h1 = hm.register_handle(_Work(True), hm.SEND, "t1", link=a)
+    h2 = hm.register_handle(_Work(False), hm.RECV, "t2")
+    assert hm.is_valid_handle(h1) and hm.get_handle_direction(h2) == "recv" and hm.get_handle_output(h1) == "t1"
+    assert hm.get_handle_link(h1) == a
+    assert hm.reap() == 1 and not hm.is_valid_handle(h1)
+    hm.wait(h2)
+    assert hm.poll(h2)
+    hm.clear_handle(h2)
+    assert hm.handles() == []

@@ -86,3 +86,13 @@ def test_static_scratch_colsum_rejects_oversize():
     assert rc != 0
     msg = lib.smpk_last_error().decode()
     assert "exceeds" in msg and str(mx) in msg
+
+
+def test_native_library_selftests_on_gpu():
+    """The core library's own checks, including the symmetric-memory round trip on the device (the counterpart of
+    the reference's in-library test_d2d(), reference test/backend/d2d_test.py:11)."""
+    from smdistributed_modelparallel_b200.backend import native_core
+
+    torch.cuda.init()
+    msg = native_core.selftest(gpu=True)
+    assert msg.startswith("ok:") and msg.endswith("symmetric memory ok"), msg
