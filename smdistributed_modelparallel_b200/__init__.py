@@ -44,6 +44,14 @@ def init(config=None):
     """Initialise the library: validate ``config`` (merged with ``SM_HP_MP_PARAMETERS``), bootstrap ranks
     from the launcher environment, open the control-plane bus, create every process group."""
     cfg = ModelParallelConfig(config)
+    for key in ("horovod", "herring"):
+        if getattr(cfg, key, False):
+            # silently training without gradient averaging would be worse than refusing (the reference itself
+            # refuses Herring: torch/allreduce/herring.py:9-73)
+            from .backend.exceptions import SMPUnsupportedError
+
+            raise SMPUnsupportedError(f"'{key}: true': data parallelism runs on the built-in NCCL reducers here; "
+                                      "set 'ddp: true' instead")
     if state.initialized:
         reset()
     core.initialize(cfg)

@@ -94,3 +94,13 @@ def test_alias_conflict_and_formula_defaults():
     # active_microbatches defaults to microbatches; a different value forces the interleaved schedule
     c = ModelParallelConfig({"pipeline_parallel_degree": 2, "microbatches": 8, "active_microbatches": 3, "pipeline": "simple"})
     assert c.active_microbatches == 3 and c.pipeline == "interleaved"
+
+
+@pytest.mark.parametrize("key", ["horovod", "herring"])
+def test_foreign_data_parallel_backends_are_refused(key):
+    """Horovod / Herring are not carried over; accepting the flag would train without gradient averaging."""
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200.backend.exceptions import SMPUnsupportedError
+
+    with pytest.raises(SMPUnsupportedError, match="ddp"):
+        smp.init({key: True})
