@@ -22,7 +22,7 @@ from torch.utils.hooks import RemovableHandle
 
 from .backend.exceptions import (BwdExecutionNotInStepFnError, FwdExecutionNotInStepFnError,
                                  ModelNotPartitionedError, MultipleDistributedModelError, NotInitializedError,
-                                 SMPValidationError)
+                                 SMPUnsupportedError, SMPValidationError)
 from .backend.logger import get_logger
 from .nn.dist_module import DistributedModule
 from .nn.utils import is_distributed_parameter, is_one_rank_parameter, is_scaled_batch_parameter
@@ -152,7 +152,10 @@ class DistributedModel(nn.Module):
         cfg, core = state.cfg, state.core
         from .parameter import materialize_delayed
 
-        materialize_delayed(self.module, local_only=lambda m: self._is_local_module(m))
+        if not cfg.zero2d_enabled():
+            materialize_delayed(self.module, local_only=lambda m: self._is_local_module(m))
+        # (sharded data parallelism: the engine materialises, shards and releases one unit at a time -
+        # parallel/sdp.py::_build - so no rank ever holds the whole model)
         dev = state.device
         if dev.type == "cuda":
             for m in self.local_modules():
@@ -355,6 +358,102 @@ class DistributedModel(nn.Module):
     def local_buffers(self, recurse=True):
         for _, b in self.local_named_buffers(recurse=recurse):
             yield b
+
+    # names as the wrapped module sees them, without a "module." prefix (reference model.py:1098-1108)
+    def named_parameters(self, *args, **kwargs):
+        return self.module.named_parameters(*args, **kwargs)
+
+    def parameters(self, *args, **kwargs):
+        return self.module.parameters(*args, **kwargs)
+
+    def named_buffers(self, *args, **kwargs):
+        return self.module.named_buffers(*args, **kwargs)
+
+    def buffers(self, *args, **kwargs):
+        return self.module.buffers(*args, **kwargs)
+
+    def is_local_buffer(self, buffer):
+        """By name or by tensor (reference model.py:1418-1428)."""
+        self._validate_partitioned()
+        if isinstance(buffer, str):
+            return any(n == buffer for n, _ in self.local_named_buffers())
+        if torch.is_tensor(buffer):
+            return any(b is buffer for _, b in self.local_named_buffers())
+        raise SMPUnsupportedError(f"is_local_buffer takes a name or a tensor, not {type(buffer).__name__}")
+
+    def get_module_for_param(self, param):
+        """The module that directly owns ``param`` (reference model.py:348-349)."""
+        for m in self.module.modules():
+            for p in m.parameters(recurse=False):
+                if p is param:
+                    return m
+        raise KeyError("parameter does not belong to this model")
+
+    def scaled_batch_reducer_named_parameters(self):
+        """Parameters whose gradients are averaged over the reduced-data-parallel group only (they already saw
+        the whole tensor-parallel group's batch; reference model.py:586-613, 1430-1432)."""
+        for n, p in self.local_named_parameters():
+            if p.requires_grad and is_scaled_batch_parameter(p):
+                yield n, p
+
+    def default_reducer_named_parameters(self):
+        """Parameters averaged over the full data-parallel group (reference model.py:1434-1436)."""
+        for n, p in self.local_named_parameters():
+            if p.requires_grad and not is_scaled_batch_parameter(p):
+                yield n, p
+
+    def virtual_named_parameters(self):
+        """Under optimizer-state sharding: this rank's slices of the flat parameter buffer, the tensors the
+        inner optimizer really updates (reference model.py:1237-1340, 1371-1373)."""
+        shard = getattr(state.optimizer, "_opt_shard", None) if state.optimizer is not None else None
+        if shard is None:
+            return
+        yield from shard.virtual_named_parameters()
+
+    def display_partition(self):
+        """Log the module tree down to the first level at which a subtree lives on one pipeline rank
+        (reference model.py:668-701).  Returns the lines."""
+        self._validate_partitioned()
+        mm = state.module_manager
+        lines = []
+
+        def ranks_below(m):
+            return {mm.get_partition(x) for x in m.modules()}
+
+        def walk(m, name, depth):
+            below = ranks_below(m)
+            if len(below) <= 1:
+                lines.append(f"{'  ' * depth}{name or 'main'}: {next(iter(below)) if below else mm.get_partition(m)}")
+                return
+            lines.append(f"{'  ' * depth}{name or 'main'}: {mm.get_partition(m)} (children on {sorted(below)})")
+            for cn, c in m.named_children():
+                walk(c, f"{name}/{cn}" if name else cn, depth + 1)
+
+        walk(self.module, "", 0)
+        if state.core.rank() == 0:
+            log = get_logger()
+            log.info("Partition assignments:")
+            for ln in lines:
+                log.info(ln)
+        return lines
+
+    def load_partition(self, partitioning_and_trace_results=None):
+        """Adopt a saved module -> pipeline-rank assignment (reference model.py:846-849)."""
+        if partitioning_and_trace_results is not None:
+            info = partitioning_and_trace_results
+            if isinstance(info, dict) and "partition_info" in info:
+                info = info["partition_info"]
+            self.load_saved_partition(info)
+
+    def get_ddp_logging_data(self):
+        """What the reducer did in the steps so far (bucket count, overlapped / trailing elements)."""
+        r = self.reducer
+        if r is None:
+            return {}
+        out = dict(getattr(r, "stats", {}))
+        out["num_buckets"] = len(getattr(r, "_hook_buckets", None) or getattr(r, "buckets", None) or [])
+        out["dp_size"] = getattr(r, "dp_size", 1)
+        return out
 
     def is_distributed_parameter(self, param):
         return is_distributed_parameter(param)

@@ -174,6 +174,9 @@ class DistributedOptimizer:
         opt = self.__dict__.get("optimizer")
         if opt is None:
             raise AttributeError(name)
+        bit16 = self.__dict__.get("_bit16")
+        if bit16 is not None and not name.startswith("_") and hasattr(type(bit16), name):
+            return getattr(bit16, name)            # master-weight inspection etc. (the 16-bit wrapper's API)
         return getattr(opt, name)
 
     # ------------------------------------------------------------------ state dicts

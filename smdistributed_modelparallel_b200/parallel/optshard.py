@@ -202,6 +202,12 @@ class OptimizerStateSharding:
                 dist.all_gather_into_tensor(self.param_buffer[a:b], self.param_buffer[sl["start"]:sl["end"]], group=group)
 
     # ------------------------------------------------------------------ checkpointing
+    def virtual_named_parameters(self):
+        """(name, fp32 master slice) for every slice of the flat buffer this rank owns - the tensors the inner
+        optimizer updates (the reference's "virtual parameters", model.py:1237-1340)."""
+        for i, sl in enumerate(self.slices):
+            yield f"{sl['region']}.group{sl['gi']}.slice{i}[{sl['start']}:{sl['end']}]", sl["master"]
+
     def shard_info(self):
         return {"slices": [{"region": s["region"], "group": s["gi"], "start": s["start"], "end": s["end"]}
                            for s in self.slices],

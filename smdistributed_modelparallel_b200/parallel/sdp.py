@@ -157,21 +157,56 @@ class ShardedDataParallelEngine:
         group_of = group_of or (lambda p: 0)
         from . import sdp_fused
         self.fused = self._want_fused and sdp_fused.supported(self)
-        sharded = {id(p) for p in self.all_params if p.numel() >= self.threshold}
-        self.persistent = [p for p in self.all_params if id(p) not in sharded]
         root = self.model.module
         names = {m: n for n, m in root.named_modules()}
         seen = set()
 
+        def is_sharded(p):
+            return p.requires_grad and p.numel() >= self.threshold
+
+        # Sharded initialisation (the reference wraps model creation in deepspeed.zero.Init for this,
+        # torch/parameter.py:23-32): with delayed parameter initialisation the model arrives here on the meta
+        # device and every unit is materialised, initialised, sharded and released in turn, so a rank never holds
+        # more than one unit in full.  Parameters are tracked by (owning module, name) slots because
+        # materialisation replaces the Parameter objects.
+        lazy = any(q.is_meta for q in root.parameters())
+        owners, slot_group = {}, {}
+
+        def index_owners(mods):
+            for mod in mods:
+                for n, q in mod.named_parameters(recurse=False):
+                    slots = owners.setdefault(id(q), [])
+                    if (mod, n) not in slots:
+                        slots.append((mod, n))
+
+        index_owners(root.modules())
+        for pid, slots in owners.items():
+            q = slots[0][0]._parameters[slots[0][1]]
+            for slot in slots:
+                slot_group[slot] = group_of(q)
+
+        def gof(q):
+            return slot_group.get(owners[id(q)][0], 0) if id(q) in owners else group_of(q)
+
+        def realise(plist):
+            if not lazy or not any(q.is_meta for q in plist):
+                return plist
+            from ..parameter import materialize_delayed
+            where = [owners[id(q)][0] for q in plist]
+            mods = {owners[id(q)][0][0] for q in plist if q.is_meta}
+            materialize_delayed(root, local_only=lambda mod: mod in mods, device=self.device)
+            index_owners(root.modules())
+            return [mod._parameters[n] for mod, n in where]
+
         def subtree_count(m):
-            return sum(p.numel() for p in m.parameters() if id(p) in sharded)
+            return sum(p.numel() for p in m.parameters() if is_sharded(p))
 
         def add_unit(m, plist, tag=""):
-            plist = [p for p in plist if id(p) in sharded and id(p) not in seen]
-            for p in plist:
-                seen.add(id(p))
-            for gi in sorted({group_of(p) for p in plist}):
-                sub = [p for p in plist if group_of(p) == gi]
+            plist = [p for p in plist if is_sharded(p) and id(p) not in seen]
+            for gi in sorted({gof(p) for p in plist}):
+                sub = realise([p for p in plist if gof(p) == gi and id(p) not in seen])
+                for p in sub:
+                    seen.add(id(p))
                 u = Unit(f"{names[m] or 'root'}{tag}#{gi}", m, sub, gi, self.degree, self.shard_rank, self.device,
                          striped=self.fused)
                 self.units.append(u)
@@ -191,6 +226,14 @@ class ShardedDataParallelEngine:
                 assign(c)
 
         assign(root)
+        if lazy:
+            from ..parameter import materialize_delayed
+            materialize_delayed(root, device=self.device)      # what is left: small (persistent) parameters, buffers
+            index_owners(root.modules())
+            self.all_params = [p for p in root.parameters() if p.requires_grad]
+        self._group_of_current = gof
+        in_units = {id(p) for u in self.units for p in u.params}
+        self.persistent = [p for p in self.all_params if id(p) not in in_units]
         by_module = OrderedDict()
         for u in self.units:
             by_module.setdefault(u.module, []).append(u)
@@ -474,7 +517,7 @@ class ShardedDataParallelEngine:
         for p in self.persistent:
             m = self.persistent_masters[p]
             m.grad = p.main_grad
-            new_groups[group_index.get(id(p), 0)].append(m)
+            new_groups[self._group_of_current(p)].append(m)
         for g, plist in zip(optimizer.param_groups, new_groups):
             g["params"] = plist
         optimizer.state.clear()

@@ -5,8 +5,9 @@ Large models must not be materialised in full on every rank before partitioning.
 storage); the initialisers that ran during construction are irrelevant because each module's
 ``reset_parameters`` (or the recorded custom initialiser) is replayed after partitioning, only for the
 modules this rank owns, directly on the target device (reference smdistributed/modelparallel/torch/
-parameter.py:35-76 records and replays initialisers; :23-32 is the sharded-init variant for SDP, which
-here is handled by the ZeRO-3 engine sharding right after materialisation).
+parameter.py:35-76 records and replays initialisers; :23-32 is the sharded-init variant for SDP: here the
+ZeRO-3 engine materialises, initialises, shards and releases one unit at a time - parallel/sdp.py::_build -
+so no rank ever holds the whole model).
 """
 
 from __future__ import annotations

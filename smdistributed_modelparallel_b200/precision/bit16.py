@@ -339,6 +339,34 @@ class Bit16_Optimizer:
                 c.data.copy_(s)
         self.copy_master_to_model()
 
+    # ------------------------------------------------------------------ inspection (reference fp16.py:242-807)
+    def get_master_params(self):
+        """fp32 master copies, one list per parameter group."""
+        self.init_master_params()
+        return [list(grp) for grp in self.fp32_from_fp16_groups]
+
+    def get_master_grads(self):
+        """fp32 gradients of the masters (still multiplied by the loss scale), aligned with the masters."""
+        masters, grads = self._master_grad_lists()
+        by_master = {id(m): g for m, g in zip(masters, grads)}
+        return [[by_master.get(id(m)) for m in grp] for grp in self.fp32_from_fp16_groups]
+
+    def inspect_master_grad_data(self):
+        """Unscaled fp32 gradients, ``None`` where a parameter has none; ``None`` altogether after an overflow
+        (the gradients are garbage then)."""
+        if self.overflow:
+            return None
+        inv = 1.0 / float(self.loss_scale)
+        return [[None if g is None else g * inv for g in grp] for grp in self.get_master_grads()]
+
+    def reload_model_params(self):
+        """The 16-bit model weights were changed from outside (a checkpoint load): refresh the masters."""
+        self.init_master_params()
+        self.copy_model_to_master()
+
+    def state_dict_for_save_checkpoint(self):
+        return self.state_dict()
+
     def copy_master_to_model(self):
         pairs = list(self._pairs())
         if pairs:

@@ -220,3 +220,46 @@ def test_fp16_dynamic_loss_scale_skips_overflowing_steps():
     assert first_ok > 0 and scales[first_ok] == scales[first_ok - 1]   # the scale stops shrinking once a step fits
     assert all(s == scales[-1] for s in scales[first_ok:])
     assert all(torch.isfinite(p).all() for p in model.module.parameters())
+
+
+def test_bit16_master_inspection():
+    """fp32 masters / master gradients of the 16-bit optimizer can be inspected (unscaled), the masters follow a
+    change of the model weights made from outside, and the Megatron-style getters of the state answer."""
+    import torch.nn as nn
+
+    smp.reset()
+    smp.init({"microbatches": 1, "bf16": True})
+    torch.manual_seed(0)
+    with smp.model_creation(dtype=torch.bfloat16):
+        net = nn.Sequential(nn.Linear(8, 16), nn.Tanh(), nn.Linear(16, 4))
+    model = smp.DistributedModel(net)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+
+    @smp.step
+    def train_step(model, x, y):
+        loss = ((model(x).float() - y) ** 2).mean()
+        model.backward(loss)
+        return loss
+
+    x, y = torch.randn(4, 8).bfloat16(), torch.randn(4, 4)
+    opt.zero_grad()
+    train_step(model, x, y)
+    inner = opt
+    masters = inner.get_master_params()
+    assert sum(len(g) for g in masters) == 4 and all(m.dtype == torch.float32 for g in masters for m in g)
+    grads = inner.inspect_master_grad_data()
+    flat = [g for grp in grads for g in grp]
+    assert all(g is not None and g.dtype == torch.float32 and torch.isfinite(g).all() for g in flat)
+    assert any(g.abs().sum() > 0 for g in flat)
+    scaled = [g for grp in inner.get_master_grads() for g in grp]
+    ratio = float(inner.loss_scale)
+    assert all(torch.allclose(a, b * ratio) for a, b in zip(scaled, flat))
+    assert set(inner.state_dict_for_save_checkpoint()) == set(opt.fp16_optimizer.state_dict())
+    with torch.no_grad():
+        net[0].weight.fill_(0.25)
+    inner.reload_model_params()
+    assert all(torch.equal(m, torch.full_like(m, 0.25)) for g in inner.get_master_params() for m in g
+               if m.shape == net[0].weight.shape)
+    st = smp.state
+    assert st.get_data_parallel_world_size() == 1 and st.get_model_parallel_world_size() == 1
+    assert st.get_data_parallel_rank() == 0 and st.get_model_parallel_rank() == 0 and not st.is_tracing()

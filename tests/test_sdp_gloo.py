@@ -155,3 +155,79 @@ def test_sdp_with_a_module_used_twice():
     for r in res:
         assert r["units"] >= 2
         assert r["worst"] < 2e-4, r["worst"]
+
+
+def _sharded_init_worker(rank, world):
+    import torch.nn as nn
+
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200 import parameter as P
+
+    os.environ["SMP_SDP_UNIT_ELEMENTS"] = "5000"
+    smp.init({"sharded_data_parallel_degree": 2, "microbatches": 2, "ddp": True,
+              "sdp_param_persistence_threshold": 100, "delayed_parameter_initialization": True})
+    # watch how much is materialised at any one time: bytes given storage minus bytes already sharded away
+    live = {"now": 0, "peak": 0}
+    orig = P._materialize_module
+
+    def counting(m, device):
+        done = orig(m, device)
+        if done:
+            live["now"] += sum(p.numel() for p in m.parameters(recurse=False))
+            live["peak"] = max(live["peak"], live["now"])
+        return done
+
+    P._materialize_module = counting
+    from smdistributed_modelparallel_b200.parallel import sdp as S
+    unit_init = S.Unit.__init__
+
+    def unit_counting(self, *a, **k):
+        unit_init(self, *a, **k)
+        live["now"] -= sum(self.numels.values())
+
+    S.Unit.__init__ = unit_counting
+    torch.manual_seed(3 + rank)                       # ranks need not agree: each keeps its own shard of its own draw
+    with smp.model_creation(dtype=None):
+        net = nn.Sequential(nn.Linear(16, 64), nn.Tanh(), nn.Linear(64, 64), nn.Tanh(), nn.Linear(64, 64),
+                            nn.Tanh(), nn.Linear(64, 4))
+    assert all(p.is_meta for p in net.parameters())
+    model = smp.DistributedModel(net)
+    opt = smp.DistributedOptimizer(torch.optim.AdamW(
+        [{"params": [p for n, p in model.named_parameters() if n.endswith("weight")], "weight_decay": 0.1},
+         {"params": [p for n, p in model.named_parameters() if n.endswith("bias")], "weight_decay": 0.0}], lr=1e-2))
+
+    @smp.step
+    def train_step(model, x, y):
+        loss = ((model(x) - y) ** 2).mean()
+        model.backward(loss)
+        return loss
+
+    g = torch.Generator().manual_seed(5)
+    x, y = torch.randn(8, 16, generator=g), torch.randn(8, 4, generator=g)
+    losses = []
+    for _ in range(6):
+        opt.zero_grad()
+        losses.append(train_step(model, x[rank * 4:(rank + 1) * 4], y[rank * 4:(rank + 1) * 4]).reduce_mean().item())
+        opt.step()
+    eng = model.sdp_engine
+    full = model.state_dict()
+    total = sum(p.numel() for p in full.values())
+    groups = [len(g["params"]) for g in opt.param_groups]
+    return {"losses": losses, "peak": live["peak"], "total": total, "units": len(eng.units),
+            "unit_groups": sorted({u.gi for u in eng.units}), "groups": groups,
+            "std": float(full["2.weight"].float().std()), "w0": full["0.weight"].float(),
+            "meta_left": sum(p.is_meta for p in net.parameters())}
+
+
+def test_sdp_sharded_initialisation():
+    """Delayed parameter initialisation under sharded data parallelism: units are materialised, initialised, sharded
+    and released one at a time (never the whole model at once); parameter groups of the optimizer survive the
+    replacement of the meta parameters; training proceeds from a sane initialisation."""
+    res = run_distributed(_sharded_init_worker, 2, timeout=300)
+    for r in res:
+        assert r["meta_left"] == 0 and r["units"] >= 3
+        assert r["peak"] < 0.7 * r["total"], (r["peak"], r["total"])
+        assert r["unit_groups"] == [0] and r["groups"][0] == r["units"] and r["groups"][1] >= 1, r
+        assert 0.02 < r["std"] < 0.2
+        assert r["losses"][-1] < r["losses"][0]
+    assert torch.equal(res[0]["w0"], res[1]["w0"])          # both ranks see the same gathered model
