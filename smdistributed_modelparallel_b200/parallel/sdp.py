@@ -202,7 +202,7 @@ class ShardedDataParallelEngine:
             return sum(p.numel() for p in m.parameters() if is_sharded(p))
 
         def add_unit(m, plist, tag=""):
-            plist = [p for p in plist if is_sharded(p) and id(p) not in seen]
+            plist = list({id(p): p for p in plist if is_sharded(p) and id(p) not in seen}.values())
             for gi in sorted({gof(p) for p in plist}):
                 sub = realise([p for p in plist if gof(p) == gi and id(p) not in seen])
                 for p in sub:

@@ -45,12 +45,17 @@ def _from_wire(obj):
     return obj
 
 
-def _entry(rank, world, port, fn, args, queue, use_cuda=False):
+def _entry(rank, world, port, fn, args, queue, use_cuda=False, env=None):
+    if env:                                  # a fork-server child starts from the server's environment
+        os.environ.update(env)
     os.environ.update({"RANK": str(rank), "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank),
                        "LOCAL_WORLD_SIZE": str(world), "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port),
                        "SMP_LOG_LEVEL": os.environ.get("SMP_LOG_LEVEL", "warning")})
     if not use_cuda:
         os.environ["CUDA_VISIBLE_DEVICES"] = ""
+        import torch
+        # tiny tensors, several ranks per machine: intra-op threads only fight one another
+        torch.set_num_threads(max(1, (os.cpu_count() or 4) // (2 * world)))
     sys.path.insert(0, ROOT)
     dump_after = float(os.environ.get("SMP_TEST_HANG_DUMP_S", "0"))
     if dump_after > 0:                       # where is every thread if the worker is still running by then?
@@ -66,10 +71,17 @@ def _entry(rank, world, port, fn, args, queue, use_cuda=False):
 
 def run_distributed(fn, world, *args, timeout=240, use_cuda=False):
     timeout = float(os.environ.get("SMP_TEST_TIMEOUT_S", timeout))
-    ctx = mp.get_context("spawn")
+    # CPU workers are forked from a server that has already imported torch (seconds per process otherwise);
+    # the server never touches torch.distributed or CUDA, so its children start clean.  GPU workers are spawned.
+    if use_cuda or os.environ.get("SMP_TEST_START_METHOD") == "spawn":
+        ctx = mp.get_context("spawn")
+    else:
+        ctx = mp.get_context("forkserver")
+        ctx.set_forkserver_preload(["torch", "numpy"])
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, q, use_cuda)) for r in range(world)]
+    env = dict(os.environ)
+    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, q, use_cuda, env)) for r in range(world)]
     for p in procs:
         p.start()
     results = {}

@@ -199,3 +199,39 @@ def test_backward_passes_per_step_accumulates_then_reduces():
     reduction; the update equals the dense model's with both batches' gradients summed."""
     res = run_distributed(_accum_worker, 2)
     assert max(res) < 2e-5, res
+
+
+def _tp_optshard_worker(rank, world, shard):
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"tensor_parallel_degree": 2, "microbatches": 2, "ddp": True, "ddp_dist_backend": "gloo", "bf16": True,
+              "shard_optimizer_state": shard})
+    torch.manual_seed(1)
+    with smp.model_creation(tensor_parallelism=True, dtype=torch.bfloat16):
+        module = smp.nn.DistributedTransformerLMHead(**CFG)
+    model = smp.DistributedModel(module)
+    opt = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2))
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    g = torch.Generator().manual_seed(10 + smp.rdp_rank())
+    out = []
+    for _ in range(3):
+        ids = torch.randint(0, CFG["vocab_size"], (4, 16), generator=g)
+        opt.zero_grad()
+        out.append(train_step(model, ids).reduce_mean().item())
+        opt.step()
+    return {"losses": out, "virtual": len(list(model.virtual_named_parameters()))}
+
+
+def test_tp2_rdp2_optimizer_state_sharding_matches_unsharded():
+    """tp2 x rdp2, bf16: distributed parameters shard their optimizer state over the two replicas, the rest over all
+    four ranks; the loss curve is bit-identical to the run that keeps the whole state everywhere."""
+    plain = run_distributed(_tp_optshard_worker, 4, False, timeout=300)
+    sharded = run_distributed(_tp_optshard_worker, 4, True, timeout=300)
+    assert plain[0]["losses"] == sharded[0]["losses"], (plain[0], sharded[0])
+    assert plain[0]["virtual"] == 0 and sharded[0]["virtual"] >= 2
