@@ -29,6 +29,7 @@ What is different (by design):
 
 from __future__ import annotations
 
+import os
 import threading
 import traceback
 from dataclasses import dataclass, field
@@ -76,6 +77,18 @@ class PipelineP2P:
         self.me = state.core.rank()
         self.links = LinkManager(state.core.pp_rank())     # one link per transfer slot, recycled every step
         self.handles = HandleManager()                     # keeps in-flight sends (and their tensors) alive
+        # static mode (reference backend/config.yaml:191-197, torch/server_queue.py:419-490): the first step of
+        # a step function records, per source rank, the sequence of tensor receptions; later steps post those
+        # receives ahead of the control message that announces them, so a sender's transfer never waits for this
+        # rank's Python to get round to the message
+        self._plans = {}            # key -> {src: [(metas key, device)]}
+        self._open = False
+        self._static = False
+        self._recording = False
+        self._key = None
+        self._seen, self._cursor, self._posted = {}, {}, {}
+        self.lookahead = max(1, int(os.environ.get("SMP_STATIC_LOOKAHEAD", "2")))
+        self.stats = {"recorded_steps": 0, "replayed_steps": 0, "preposted": 0}
 
     def _wire(self, t):
         t = t.detach()
@@ -100,13 +113,13 @@ class PipelineP2P:
         message order); the current stream waits for them now, or - with ``defer`` - when the caller later runs
         the returned ``finish()`` (results stashed for a task that resumes later must not stall whatever the
         compute stream is doing meanwhile)."""
-        group = self.state.pp_p2p_groups[(src, self.me)]
-        out, works = [], []
-        for shape, dtype in metas:
-            wire_dtype = torch.uint8 if dtype == torch.bool else dtype
-            buf = torch.empty(shape, dtype=wire_dtype, device=device)
-            works.append(dist.irecv(buf, src=src, group=group))
-            out.append(buf)
+        metas = [(tuple(shape), dtype) for shape, dtype in metas]
+        if self._static and self._open and not self._recording:
+            out, works = self._take_preposted(tuple(metas), src)
+        else:
+            if self._static and self._open:
+                self._seen.setdefault(src, []).append((tuple(metas), device))
+            out, works = self._post(metas, src, device)
 
         def finish():
             for w in works:
@@ -115,12 +128,77 @@ class PipelineP2P:
 
         return finish if defer else finish()
 
+    def _post(self, metas, src, device):
+        group = self.state.pp_p2p_groups[(src, self.me)]
+        out, works = [], []
+        for shape, dtype in metas:
+            wire_dtype = torch.uint8 if dtype == torch.bool else dtype
+            buf = torch.empty(shape, dtype=wire_dtype, device=device)
+            works.append(dist.irecv(buf, src=src, group=group))
+            out.append(buf)
+        return out, works
+
+    # ------------------------------------------------------------------ static mode
+    def begin_step(self, key):
+        cfg = self.state.cfg
+        # posting ahead needs the order of receptions from each source to repeat exactly.  It does when stages
+        # only answer the leader; with fast-mode chains over three or more stages a stage is fed by two sources and
+        # the order of its answers depends on timing, so the dynamic protocol stays in charge there.
+        self._static = bool(getattr(cfg, "static_mode", False)) and not (
+            getattr(cfg, "fast_mode", False) and self.state.core.pp_size() > 2)
+        if not self._static:
+            return
+        if self._open:                      # the previous step never reached drain(): what was learnt is suspect
+            self._plans.clear()
+        self._open, self._key = True, key
+        plan = self._plans.get(key)
+        self._recording = plan is None
+        self._seen, self._cursor, self._posted = {}, {}, {}
+        if plan is not None:
+            for src in plan:
+                self._prepost(src)
+
+    def _prepost(self, src):
+        plan = self._plans[self._key][src]
+        posted = self._posted.setdefault(src, [])
+        nxt = self._cursor.get(src, 0) + len(posted)
+        while len(posted) < self.lookahead and nxt < len(plan):
+            metas, device = plan[nxt]
+            posted.append(self._post(list(metas), src, device))
+            self.stats["preposted"] += 1
+            nxt += 1
+
+    def _take_preposted(self, metas, src):
+        plan = self._plans[self._key].get(src, [])
+        i = self._cursor.get(src, 0)
+        if i >= len(plan) or plan[i][0] != metas:
+            raise SMPRuntimeError(
+                f"static_mode: reception {i} from rank {src} differs from the recorded step "
+                f"({metas if i >= len(plan) else (plan[i][0], metas)}); static mode needs identical steps")
+        out, works = self._posted[src].pop(0)
+        self._cursor[src] = i + 1
+        self._prepost(src)
+        return out, works
+
     def drain(self):
         """End of step: every send has left; the links are free for the next step."""
         for h in self.handles.handles():
             self.handles.wait(h)
             self.handles.clear_handle(h)
         self.links.reset()
+        if self._static and self._open:
+            self._open = False
+            if self._recording:
+                self._plans[self._key] = self._seen
+                self.stats["recorded_steps"] += 1
+            else:
+                for src, plan in self._plans[self._key].items():
+                    if self._cursor.get(src, 0) != len(plan):
+                        self._plans.clear()
+                        raise SMPRuntimeError(
+                            f"static_mode: {self._cursor.get(src, 0)} receptions from rank {src} this step, "
+                            f"{len(plan)} in the recorded one; static mode needs identical steps")
+                self.stats["replayed_steps"] += 1
 
 
 _task_local = threading.local()
@@ -441,7 +519,11 @@ class ExecutionServer:
         dev = self.state.device
         if isinstance(msg, ForwardRequest):
             metas = [(s.shape, s.dtype) for s in stubs_of(msg.skeleton)]
-            tensors = self.p2p.recv(metas, src, dev)
+            try:
+                tensors = self.p2p.recv(metas, src, dev)
+            except Exception:
+                self.comm.server_send(ForwardResult(msg.mb, msg.call_id, None, traceback.format_exc()), msg.requester)
+                raise
             self._serve_forward(src, msg, tensors)
         elif isinstance(msg, ForwardResult):
             metas = [(s.shape, s.dtype) for s in stubs_of(msg.skeleton)] if msg.error is None else []
@@ -656,6 +738,7 @@ class ExecutionServer:
         if not self.partitioned:
             self._partition(step_fn, args, kwargs, num_mb)
         self._done_msg = None
+        self.p2p.begin_step((st.current_step_func_id, torch.is_grad_enabled(), num_mb))
         pipe = st.pipeline
         pipe.init_step()
         group = self.core.get_pp_group()

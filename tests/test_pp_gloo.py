@@ -141,13 +141,13 @@ def test_pp2_tp2_tracks_dense(window, prescaled):
         assert abs(mean - ol.item()) < 3e-5, (it, mean, ol.item())
 
 
-def _pp4_worker(rank, world, fast_mode=False):
+def _pp4_worker(rank, world, fast_mode=False, static_mode=False):
     import copy
 
     import smdistributed_modelparallel_b200 as smp
 
     smp.init({"pipeline_parallel_degree": 4, "microbatches": 4, "ddp": False, "active_microbatches": 3,
-              "fast_mode": fast_mode})
+              "fast_mode": fast_mode, "static_mode": static_mode})
     torch.manual_seed(7)
     cfg = dict(CFG, num_layers=8)
     module = smp.nn.DistributedTransformerLMHead(**cfg)
@@ -176,16 +176,17 @@ def _pp4_worker(rank, world, fast_mode=False):
     opt.step()
     loss2 = train_step(model, ids).reduce_mean().item()
     return {"loss": loss, "oracle": ol.item(), "worst": worst, "n_local": n_local, "layers": layers,
-            "loss2": loss2, "hop_bytes": smp.state.module_manager.comm_volume_bytes}
+            "loss2": loss2, "hop_bytes": smp.state.module_manager.comm_volume_bytes,
+            "static": dict(smp.state.exec_server.p2p.stats)}
 
 
-@pytest.mark.parametrize("fast_mode", [False, True])
-def test_pp4_matches_dense(fast_mode):
+@pytest.mark.parametrize("fast_mode,static_mode", [(False, False), (True, False), (False, True)])
+def test_pp4_matches_dense(fast_mode, static_mode):
     """Four pipeline stages (reference test/torch/mpi_4ps): the layer stack is cut into four contiguous chunks
     served in sequence; loss and every local gradient match the dense model.  In fast mode the chunks hand
     their outputs to one another directly (and the gradients walk back the same way), so the leader moves
     far fewer bytes."""
-    res = run_distributed(_pp4_worker, 4, fast_mode, timeout=420)
+    res = run_distributed(_pp4_worker, 4, fast_mode, static_mode, timeout=420)
     for r in res:
         assert abs(r["loss"] - r["oracle"]) < 1e-5, r
         assert r["worst"] < 1e-5, r
@@ -193,6 +194,9 @@ def test_pp4_matches_dense(fast_mode):
         assert r["loss2"] < r["loss"]
     layers = res[0]["layers"]
     assert sorted(set(layers)) == [0, 1, 2, 3] and layers == sorted(layers), layers
+    if static_mode:                      # the second step replayed the record of the first on every stage
+        assert all(r["static"]["replayed_steps"] == 1 and r["static"]["preposted"] > 0 for r in res), res
+        return
     test_pp4_matches_dense.leader_bytes[fast_mode] = res[0]["hop_bytes"]
     if len(test_pp4_matches_dense.leader_bytes) == 2:
         assert test_pp4_matches_dense.leader_bytes[True] < 0.6 * test_pp4_matches_dense.leader_bytes[False]
@@ -385,3 +389,80 @@ def test_step_failure_reaches_every_pipeline_rank():
     res = run_distributed(_failing_step_worker, 2, timeout=180)
     assert "deliberate failure" in res[0]["error"] and res[0]["error"].startswith("ValueError")
     assert "deliberate failure" in res[1]["error"], res[1]
+
+
+def _static_worker(rank, world, static_mode):
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 4, "ddp": False, "static_mode": static_mode})
+    torch.manual_seed(7)
+    model = smp.DistributedModel(smp.nn.DistributedTransformerLMHead(**CFG))
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    @smp.step
+    def eval_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        return loss
+
+    g = torch.Generator().manual_seed(3)
+    losses = []
+    for i in range(4):
+        ids = torch.randint(0, CFG["vocab_size"], (8, 16), generator=g)
+        opt.zero_grad()
+        losses.append(train_step(model, ids).reduce_mean().item())
+        opt.step()
+        if i % 2 == 1:
+            with torch.no_grad():
+                losses.append(eval_step(model, ids).reduce_mean().item())
+    stats = dict(smp.state.exec_server.p2p.stats)
+    return {"losses": losses, "stats": stats}
+
+
+def test_static_mode_preposts_receives_and_changes_nothing():
+    """``static_mode``: the first step of each step function records the receptions per source, later steps post
+    them ahead of the announcing message; results are identical to the dynamic protocol, the train and eval step
+    functions keep separate records."""
+    plain = run_distributed(_static_worker, 2, False, timeout=240)
+    static = run_distributed(_static_worker, 2, True, timeout=240)
+    assert plain[0]["losses"] == static[0]["losses"], (plain[0]["losses"], static[0]["losses"])
+    for r in static:
+        assert r["stats"]["recorded_steps"] == 2 and r["stats"]["replayed_steps"] == 4, r["stats"]
+        assert r["stats"]["preposted"] > 0
+    assert all(r["stats"]["preposted"] == 0 for r in plain)
+
+
+def test_static_mode_refuses_a_step_that_differs_from_its_record():
+    from types import SimpleNamespace
+
+    from smdistributed_modelparallel_b200.backend.exceptions import SMPRuntimeError
+    from smdistributed_modelparallel_b200.runtime.server import PipelineP2P
+
+    st = SimpleNamespace(core=SimpleNamespace(rank=lambda: 0, pp_rank=lambda: 0), cfg=SimpleNamespace(static_mode=True, fast_mode=False))
+    p2p = PipelineP2P(st)
+    posted = []
+    p2p._post = lambda metas, src, device: (posted.append((tuple(metas), src)) or ([None] * len(metas), []))
+    a, b = [((2, 4), torch.float32)], [((2, 8), torch.float32), ((2,), torch.int64)]
+    p2p.begin_step("k")
+    p2p.recv(a, 1, "cpu")
+    p2p.recv(b, 1, "cpu")
+    p2p.recv(a, 1, "cpu")
+    p2p.drain()
+    assert p2p.stats["recorded_steps"] == 1 and len(posted) == 3
+    p2p.begin_step("k")                              # replay: the first two receptions are posted up front
+    assert len(posted) == 5 and posted[3:] == [(tuple(a), 1), (tuple(b), 1)]
+    p2p.recv(a, 1, "cpu")
+    assert len(posted) == 6                          # ... and the window slides as they are consumed
+    p2p.recv(b, 1, "cpu")
+    with pytest.raises(SMPRuntimeError, match="static_mode"):
+        p2p.recv(b, 1, "cpu")                        # the record says `a` comes third
+    p2p._open = False
+    p2p.begin_step("k")
+    p2p.recv(a, 1, "cpu")
+    with pytest.raises(SMPRuntimeError, match="identical steps"):
+        p2p.drain()                                  # fewer receptions than recorded
