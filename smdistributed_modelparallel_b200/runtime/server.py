@@ -67,8 +67,46 @@ class Boundary:
     in_requires: list
 
 
+_HOST_TX_BASE = 1 << 40       # transaction ids of tensors that travel over the host bus (even: not a user-API id)
+
+
+class _HostRecv:
+    """A tensor reception over the host message bus, shaped like a ``dist.Work``."""
+
+    def __init__(self, comm, src, tx, buf):
+        self.comm, self.src, self.tx, self.buf, self.done = comm, src, tx, buf, False
+
+    def is_completed(self):
+        return self.done or self.comm.poll_recv_from_global(self.src, self.tx)
+
+    def wait(self):
+        if self.done:
+            return
+        raw = self.comm.wait_recv_from_global(self.src, self.tx, depickle=False)
+        if self.buf.numel():
+            flat = torch.frombuffer(bytearray(raw), dtype=torch.uint8)
+            self.buf.copy_(flat.view(self.buf.dtype).reshape(self.buf.shape))
+        self.done = True
+
+
+class _HostSent:
+    def __init__(self, comm, tx):
+        self.comm, self.tx = comm, tx
+
+    def is_completed(self):
+        return True                     # the bus copied the bytes when the send was queued
+
+    def wait(self):
+        self.comm.wait_transaction(self.tx)
+
+
 class PipelineP2P:
-    """Tensor transport between pipeline ranks: one 2-rank group per ordered (src, dst) pair."""
+    """Tensor transport between pipeline ranks: one 2-rank group per ordered (src, dst) pair.
+
+    With ``SMP_DISABLE_D2D=1`` (the reference's switch for its GPU-to-GPU transport, backend/core.py:239-242) or
+    for a pair without a process group, tensors fall back to the host message bus: staged through host memory
+    and sent as raw bytes under per-pair transaction ids (the role of the reference's MPI tensor fallback,
+    test/backend/test_d2d_send_recv.py:63-86)."""
 
     def __init__(self, state):
         from .links import HandleManager, LinkManager
@@ -77,6 +115,9 @@ class PipelineP2P:
         self.me = state.core.rank()
         self.links = LinkManager(state.core.pp_rank())     # one link per transfer slot, recycled every step
         self.handles = HandleManager()                     # keeps in-flight sends (and their tensors) alive
+        self.host_only = os.environ.get("SMP_DISABLE_D2D", "0") not in ("0", "", "false")
+        self._host_tx = {}                                 # (src, dst) -> tensors moved over the bus so far
+        self.host_stats = {"sent": 0, "received": 0, "bytes": 0}
         # static mode (reference backend/config.yaml:191-197, torch/server_queue.py:419-490): the first step of
         # a step function records, per source rank, the sequence of tensor receptions; later steps post those
         # receives ahead of the control message that announces them, so a sender's transfer never waits for this
@@ -96,14 +137,32 @@ class PipelineP2P:
             t = t.to(torch.uint8)
         return t if t.is_contiguous() else t.contiguous()
 
+    def _next_host_tx(self, src, dst):
+        n = self._host_tx.get((src, dst), 0)
+        self._host_tx[(src, dst)] = n + 1
+        # unique per ordered pair and per tensor; both ends count the same sequence
+        return _HOST_TX_BASE + 2 * ((n << 16) | (src & 0xFF) << 8 | (dst & 0xFF))
+
+    def _via_host(self, a, b):
+        return self.host_only or (a, b) not in self.state.pp_p2p_groups
+
     def send(self, tensors, dst):
-        group = self.state.pp_p2p_groups[(self.me, dst)]
+        host = self._via_host(self.me, dst)
+        group = None if host else self.state.pp_p2p_groups[(self.me, dst)]
         nbytes = 0
         for t in tensors:
             w = self._wire(t)
             n = w.numel() * w.element_size()
-            work = dist.isend(w, dst=dst, group=group)
-            self.handles.register_handle(work, self.handles.SEND, w, self.links.get_link(n))
+            if host:
+                tx = self._next_host_tx(self.me, dst)
+                raw = w.reshape(-1).view(torch.uint8).cpu().numpy().tobytes() if n else b""
+                self.state.comm.async_send_global(raw, dst, tx, do_pickle=False)
+                work, keep = _HostSent(self.state.comm, tx), None
+                self.host_stats["sent"] += 1
+                self.host_stats["bytes"] += n
+            else:
+                work, keep = dist.isend(w, dst=dst, group=group), w
+            self.handles.register_handle(work, self.handles.SEND, keep, self.links.get_link(n))
             nbytes += n
         self.state.module_manager.record_hop(nbytes)
         self.handles.reap(self.handles.SEND)
@@ -129,12 +188,17 @@ class PipelineP2P:
         return finish if defer else finish()
 
     def _post(self, metas, src, device):
-        group = self.state.pp_p2p_groups[(src, self.me)]
+        host = self._via_host(src, self.me)
+        group = None if host else self.state.pp_p2p_groups[(src, self.me)]
         out, works = [], []
         for shape, dtype in metas:
             wire_dtype = torch.uint8 if dtype == torch.bool else dtype
             buf = torch.empty(shape, dtype=wire_dtype, device=device)
-            works.append(dist.irecv(buf, src=src, group=group))
+            if host:
+                works.append(_HostRecv(self.state.comm, src, self._next_host_tx(src, self.me), buf))
+                self.host_stats["received"] += 1
+            else:
+                works.append(dist.irecv(buf, src=src, group=group))
             out.append(buf)
         return out, works
 

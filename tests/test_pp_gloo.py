@@ -421,7 +421,7 @@ def _static_worker(rank, world, static_mode):
             with torch.no_grad():
                 losses.append(eval_step(model, ids).reduce_mean().item())
     stats = dict(smp.state.exec_server.p2p.stats)
-    return {"losses": losses, "stats": stats}
+    return {"losses": losses, "stats": stats, "host": dict(smp.state.exec_server.p2p.host_stats)}
 
 
 def test_static_mode_preposts_receives_and_changes_nothing():
@@ -466,3 +466,17 @@ def test_static_mode_refuses_a_step_that_differs_from_its_record():
     p2p.recv(a, 1, "cpu")
     with pytest.raises(SMPRuntimeError, match="identical steps"):
         p2p.drain()                                  # fewer receptions than recorded
+
+
+def test_host_bus_fallback_for_pipeline_tensors(monkeypatch):
+    """``SMP_DISABLE_D2D=1``: pipeline tensors travel over the host message bus instead of the p2p process groups
+    (the reference's MPI fallback of its D2D transport); same numbers, with and without static mode."""
+    plain = run_distributed(_static_worker, 2, False, timeout=240)
+    monkeypatch.setenv("SMP_DISABLE_D2D", "1")
+    host = run_distributed(_static_worker, 2, False, timeout=240)
+    host_static = run_distributed(_static_worker, 2, True, timeout=240)
+    assert plain[0]["losses"] == host[0]["losses"] == host_static[0]["losses"]
+    assert all(r["host"]["sent"] == 0 for r in plain)
+    for r in host + host_static:
+        assert r["host"]["sent"] > 0 and r["host"]["received"] > 0 and r["host"]["bytes"] > 0
+    assert host_static[0]["stats"]["replayed_steps"] == 4
