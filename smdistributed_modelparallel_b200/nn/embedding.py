@@ -22,7 +22,8 @@ from .utils import (allgather_for_tp, get_local_channels, get_start_pos_for_slic
 class DistributedEmbedding(DistributedModule):
     def __init__(self, num_embeddings, embedding_dim, padding_idx=None, max_norm=None, norm_type=2.0,
                  scale_grad_by_freq=False, sparse=False, _weight=None, initializer_range=0.02, vocab_parallel=True,
-                 _skip_allgather=False, _output_full_batch=False, dtype=None, device=None):
+                 _skip_allgather=False, _output_full_batch=False, dtype=None, device=None,
+                 _skip_scatter_and_merge=False):
         super().__init__()
         assert max_norm is None and not scale_grad_by_freq and not sparse, \
             "max_norm / scale_grad_by_freq / sparse are not supported by DistributedEmbedding"
@@ -31,6 +32,8 @@ class DistributedEmbedding(DistributedModule):
         self.vocab_parallel = vocab_parallel
         self._skip_allgather = _skip_allgather      # inputs are already identical on every tp rank
         self._output_full_batch = _output_full_batch
+        # hidden-parallel only: keep the looked-up columns [tokens, H/t] (reference nn/embedding.py:195)
+        self._skip_scatter_and_merge = _skip_scatter_and_merge
         if vocab_parallel:
             self.local_num_embeddings = get_local_channels(num_embeddings)
             self.vocab_start_idx = get_start_pos_for_slicing(num_embeddings)
@@ -84,6 +87,9 @@ class DistributedEmbedding(DistributedModule):
             return out.reshape(*shape, self.embedding_dim)
         # hidden-parallel: every rank looks up all tokens for its columns, then tokens <-> columns all-to-all
         part = F.embedding(full_ids, self.weight)                    # [T, H/t]
+        if self._skip_scatter_and_merge:
+            lead = shape if self._skip_allgather else (t * shape[0], *shape[1:])
+            return part.reshape(*lead, part.shape[-1])
         from .utils import scatter_and_merge_for_tp
         out = scatter_and_merge_for_tp(part, split_dim=0, merge_dim=1)   # [T/t, H]
         if self._skip_allgather:

@@ -93,9 +93,17 @@ class DistributedLayerNorm(DistributedModule):
     """LayerNorm whose hidden dimension is split across the tensor-parallel group (``optimize=memory``
     activations ``[B, S, H/t]``).  Parameters hold the local ``H/t`` slice."""
 
-    def __init__(self, hidden_size: int, eps: float = 1e-5):
+    def __init__(self, hidden_size=None, eps: float = 1e-5, normalized_shape=None):
         super().__init__()
+        if hidden_size is None:                       # the reference's argument name (nn/layer_norm.py:108)
+            hidden_size = normalized_shape
+        if isinstance(hidden_size, (tuple, list, torch.Size)):
+            if len(hidden_size) != 1:
+                raise ValueError("DistributedLayerNorm normalises over the last (hidden) dimension only")
+            hidden_size = int(hidden_size[0])
         self.hidden_size = hidden_size
+        self.normalized_shape = torch.Size([get_local_channels(hidden_size)])
+        self.orig_last_dim = hidden_size
         self.local_hidden_size = get_local_channels(hidden_size)
         self.eps = eps
         with initialize_with_output_partition(self):

@@ -19,8 +19,12 @@ from .utils import (get_local_channels, get_split_shapes, initialize_with_input_
 
 
 class DistributedLinear(DistributedModule):
-    def __init__(self, in_features, out_features, bias=True, dtype=None, device=None):
+    def __init__(self, in_features=None, out_features=None, bias=True, dtype=None, device=None,
+                 input_features=None, output_features=None):
         super().__init__()
+        # the reference names these input_features / output_features (nn/linear.py:25)
+        in_features = input_features if in_features is None else in_features
+        out_features = output_features if out_features is None else out_features
         self.in_features, self.out_features = in_features, out_features
         self.local_in_features = get_local_channels(in_features)
         with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):

@@ -97,7 +97,9 @@ def clip_grad_norm_fp32(params_and_grads, max_norm, norm_type=2.0):
 
 class Bit16_Optimizer:
     def __init__(self, init_optimizer, model=None, static_loss_scale=1.0, dynamic_loss_scale=False,
-                 dynamic_loss_args=None, verbose=False, use_smp=True, shard_optimizer_state=False, bf16=False):
+                 dynamic_loss_args=None, verbose=False, use_smp=True, shard_optimizer_state=False, bf16=False,
+                 params_have_main_grad=None):
+        # params_have_main_grad: accepted for compatibility; fp32 main_grad buffers are detected per parameter
         self.optimizer = init_optimizer
         self.model = model
         self.bf16 = bf16
