@@ -231,3 +231,62 @@ def test_sdp_sharded_initialisation():
         assert 0.02 < r["std"] < 0.2
         assert r["losses"][-1] < r["losses"][0]
     assert torch.equal(res[0]["w0"], res[1]["w0"])          # both ranks see the same gathered model
+
+
+def _sdp_groups_resume_worker(rank, world, d):
+    import smdistributed_modelparallel_b200 as smp
+
+    os.environ["SMP_SDP_UNIT_ELEMENTS"] = "5000"
+    smp.init({"sharded_data_parallel_degree": 2, "microbatches": 2, "ddp": True, "bf16": True,
+              "sdp_param_persistence_threshold": 100, "delayed_parameter_initialization": True})
+
+    def build(seed):
+        torch.manual_seed(seed)
+        with smp.model_creation(dtype=torch.bfloat16):
+            m = smp.nn.DistributedTransformerLMHead(**CFG)
+        model = smp.DistributedModel(m)
+        decay = [p for _, p in model.named_parameters() if p.dim() > 1]
+        rest = [p for _, p in model.named_parameters() if p.dim() <= 1]
+        opt = smp.DistributedOptimizer(torch.optim.AdamW(
+            [{"params": decay, "weight_decay": 0.1}, {"params": rest, "weight_decay": 0.0}], lr=1e-2))
+        return model, opt
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    def run(model, opt, n, seed):
+        g = torch.Generator().manual_seed(seed + rank)
+        out = []
+        for _ in range(n):
+            ids = torch.randint(0, CFG["vocab_size"], (4, 16), generator=g)
+            opt.zero_grad()
+            out.append(train_step(model, ids).reduce_mean().item())
+            opt.step()
+        return out
+
+    model, opt = build(1)
+    run(model, opt, 2, 5)
+    smp.save_checkpoint(d, tag="s", partial=True, model=model, optimizer=opt)
+    want = run(model, opt, 2, 9)
+    smp.reset()
+    model2, opt2 = build(2)
+    smp.resume_from_checkpoint(d, tag="s", partial=True)
+    got = run(model2, opt2, 2, 9)
+    return {"want": want, "got": got, "groups": [len(g["params"]) for g in opt2.param_groups],
+            "decay": [g["weight_decay"] for g in opt2.param_groups]}
+
+
+def test_sdp_resume_with_parameter_groups_and_sharded_initialisation():
+    """Sharded initialisation + two optimizer parameter groups + partial checkpoint: the resumed run (built from
+    another seed, parameters still on the meta device when the checkpoint is requested) continues bit-identically
+    and keeps its groups."""
+    import tempfile
+
+    with tempfile.TemporaryDirectory() as d:
+        res = run_distributed(_sdp_groups_resume_worker, 2, d, timeout=300)
+    for r in res:
+        assert r["want"] == r["got"], r
+        assert r["decay"] == [0.1, 0.0] and all(n > 0 for n in r["groups"])
