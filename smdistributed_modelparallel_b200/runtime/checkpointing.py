@@ -165,13 +165,8 @@ def _chunks(n, strategy):
     raise CheckpointingConfigError(f"unknown checkpointing strategy {strategy!r}")
 
 
-def checkpoint_sequential(sequential, input, strategy="each", preserve_rng_state=True, pack_args_as_tuple=False):
-    """Checkpoint an ``nn.Sequential`` in groups of layers: ``each`` layer separately, all layers as one
-    ``contiguous`` block, or ``group_N`` layers at a time."""
-    if not isinstance(sequential, nn.Sequential):
-        raise CheckpointingConfigError("checkpoint_sequential expects an nn.Sequential")
-    layers = list(sequential.children())
-
+def checkpoint_layers(layers, input, strategy="each", preserve_rng_state=True, pack_args_as_tuple=False):
+    """Run ``layers`` one after another, checkpointing them in groups chosen by ``strategy``."""
     def run(a, b):
         def fn(x):
             for layer in layers[a:b]:
@@ -183,6 +178,21 @@ def checkpoint_sequential(sequential, input, strategy="each", preserve_rng_state
     for a, b in _chunks(len(layers), strategy):
         x = checkpoint(run(a, b), x, preserve_rng_state=preserve_rng_state)
     return x
+
+
+def checkpoint_sequential(sequential, input, strategy="each", preserve_rng_state=True, pack_args_as_tuple=False):
+    """Checkpoint an ``nn.Sequential`` in groups of layers: ``each`` layer separately, all layers as one
+    ``contiguous`` block, or ``group_N`` layers at a time.  When the children live on several pipeline ranks
+    the chain is cut at the partition boundaries and every rank checkpoints its own run of layers (reference
+    torch/patches/sequential.py: chain splitting across partitions)."""
+    if not isinstance(sequential, nn.Sequential):
+        raise CheckpointingConfigError("checkpoint_sequential expects an nn.Sequential")
+    from ..state_mod import state
+
+    server = getattr(state, "exec_server", None)
+    if server is not None and sequential in getattr(server, "_orig_forward", {}) and state.core.pp_size() > 1:
+        return server.run_sequential(sequential, input, (strategy, preserve_rng_state, pack_args_as_tuple))
+    return checkpoint_layers(list(sequential.children()), input, strategy, preserve_rng_state, pack_args_as_tuple)
 
 
 def apply_configured_checkpointing(root: nn.Module):

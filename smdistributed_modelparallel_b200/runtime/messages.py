@@ -62,6 +62,7 @@ class ForwardRequest:
     # output goes straight to the next of them and only the last one answers the requester
     chain: tuple = ()
     prev_hop: int | None = None   # the chain stage this request came from (None: from the requester)
+    autocast: tuple | None = None  # (device type, dtype) when the caller runs under torch.autocast
 
 
 @dataclass

@@ -265,6 +265,24 @@ class PipelineP2P:
                 self.stats["replayed_steps"] += 1
 
 
+def _autocast_state(device_type):
+    for dt in dict.fromkeys((device_type, "cuda", "cpu")):
+        try:
+            if torch.is_autocast_enabled(dt):
+                return (dt, torch.get_autocast_dtype(dt))
+        except RuntimeError:
+            continue
+    return None
+
+
+def _autocast_ctx(state):
+    import contextlib
+
+    if not state:
+        return contextlib.nullcontext()
+    return torch.autocast(state[0], dtype=state[1])
+
+
 _task_local = threading.local()
 
 
@@ -519,50 +537,67 @@ class ExecutionServer:
         return forward
 
     def _make_sequential_forward(self, seq):
+        return lambda inp: self.run_sequential(seq, inp)
+
+    def _span_ckpt(self, seq, ckpt):
+        """(strategy, preserve_rng_state, pack_args_as_tuple) in force for a run of ``seq``'s layers, or None."""
+        if ckpt is not None:
+            return tuple(ckpt)
+        cfg = self.state.module_manager.get_checkpoint_config(seq)
+        if cfg is not None and cfg.enabled:
+            return (cfg.strategy, cfg.preserve_rng_state, cfg.pack_args_as_tuple)
+        return None
+
+    @staticmethod
+    def _run_layers(layers, x, ckpt):
+        if ckpt is not None and torch.is_grad_enabled():
+            from .checkpointing import checkpoint_layers
+            return checkpoint_layers(layers, x, *ckpt)
+        for c in layers:
+            x = c(x)
+        return x
+
+    def run_sequential(self, seq, inp, ckpt=None):
+        """Forward of an ``nn.Sequential`` whose children live on several pipeline ranks: consecutive children
+        of one rank run as one chunk, here or as one remote call; activation checkpointing (configured for the
+        module, or asked for through ``smp.checkpoint_sequential``) applies to every chunk where it runs."""
         name = self.state.module_manager.get_module_name(seq)
         part = self.state.module_manager.get_partition
+        ckpt = self._span_ckpt(seq, ckpt)
+        kids = list(seq.children())
+        i, n = 0, len(kids)
+        while i < n:
+            r = part(kids[i])
+            j = i
+            while j < n and part(kids[j]) == r:
+                j += 1
+            if r == self.pp_rank:
+                inp = self._run_layers(kids[i:j], inp, ckpt)
+            else:
+                # fast mode (reference backend/config.yaml:183-190, torch/serialization.py:365-425): when
+                # the chunks that follow live on further ranks, the output of one goes straight to the
+                # next instead of child -> parent -> child; only the last one answers
+                chain, seen, first_end = [], {r}, j
+                while self.state.cfg.fast_mode and j < n:
+                    r2 = part(kids[j])
+                    if r2 == self.pp_rank or r2 in seen:
+                        break
+                    k = j
+                    while k < n and part(kids[k]) == r2:
+                        k += 1
+                    chain.append((self.core.pp_rank_to_rank(r2), (j, k)))
+                    seen.add(r2)
+                    j = k
+                inp = self._remote_forward(name, (i, first_end), self.core.pp_rank_to_rank(r), (inp,), {},
+                                           tuple(chain), ckpt)
+            i = j
+        return inp
 
-        def forward(inp):
-            kids = list(seq.children())
-            i, n = 0, len(kids)
-            while i < n:
-                r = part(kids[i])
-                j = i
-                while j < n and part(kids[j]) == r:
-                    j += 1
-                if r == self.pp_rank:
-                    for c in kids[i:j]:
-                        inp = c(inp)
-                else:
-                    # fast mode (reference backend/config.yaml:183-190, torch/serialization.py:365-425): when
-                    # the chunks that follow live on further ranks, the output of one goes straight to the
-                    # next instead of child -> parent -> child; only the last one answers
-                    chain, seen, first_end = [], {r}, j
-                    while self.state.cfg.fast_mode and j < n:
-                        r2 = part(kids[j])
-                        if r2 == self.pp_rank or r2 in seen:
-                            break
-                        k = j
-                        while k < n and part(kids[k]) == r2:
-                            k += 1
-                        chain.append((self.core.pp_rank_to_rank(r2), (j, k)))
-                        seen.add(r2)
-                        j = k
-                    inp = self._remote_forward(name, (i, first_end), self.core.pp_rank_to_rank(r), (inp,), {},
-                                               tuple(chain))
-                i = j
-            return inp
-
-        return forward
-
-    def _run_local(self, module_name, span, args, kwargs):
+    def _run_local(self, module_name, span, args, kwargs, ckpt=None):
         mm = self.state.module_manager
         m = mm.get_module(module_name)
         if span is not None:
-            x = args[0]
-            for c in list(m.children())[span[0]:span[1]]:
-                x = c(x)
-            return x
+            return self._run_layers(list(m.children())[span[0]:span[1]], args[0], ckpt)
         return m(*args, **kwargs)     # the dispatcher sees partition == this rank and runs the real forward
 
     # ================================================================== message pump
@@ -628,14 +663,14 @@ class ExecutionServer:
         return msg, finish()
 
     # ================================================================== forward across ranks
-    def _remote_forward(self, module_name, span, owner, args, kwargs, chain=()):
+    def _remote_forward(self, module_name, span, owner, args, kwargs, chain=(), ckpt=None):
         st = self.state
         mb = st.microbatch
         skel, tensors = stubify((args, kwargs))
         call_id = self._new_call_id(mb)
         grad_on = torch.is_grad_enabled()
-        req = ForwardRequest(mb, call_id, module_name if span is None else (module_name, span), skel, grad_on,
-                             self.me, chain)
+        req = ForwardRequest(mb, call_id, module_name if span is None else (module_name, span, ckpt), skel, grad_on,
+                             self.me, chain, None, _autocast_state(st.device.type))
         self.core.timeline_record_pipeline_event(mb, f"fwd_req {module_name}")
         self.comm.server_send(req, owner)
         self.p2p.send(tensors, owner)
@@ -659,7 +694,7 @@ class ExecutionServer:
         st = self.state
         prev_mb = st.microbatch
         st.microbatch = req.mb
-        name, span = (req.module_name, None) if isinstance(req.module_name, str) else req.module_name
+        name, span, ckpt = (req.module_name, None, None) if isinstance(req.module_name, str) else req.module_name
         try:
             leaves = []
             for stub, t in zip(stubs_of(req.skeleton), tensors):
@@ -668,8 +703,9 @@ class ExecutionServer:
                 leaves.append(t)
             args, kwargs = destubify(req.skeleton, leaves)
             self.core.timeline_record_pipeline_event(req.mb, f"fwd_exec {name}")
-            with torch.set_grad_enabled(req.grad_enabled):
-                out = self._run_local(name, span, args, kwargs)
+            # the caller's autocast region extends over the modules it calls, wherever they live
+            with torch.set_grad_enabled(req.grad_enabled), _autocast_ctx(req.autocast):
+                out = self._run_local(name, span, args, kwargs, ckpt)
             if req.chain:
                 (nxt, nxt_span), rest = req.chain[0], tuple(req.chain[1:])
                 skel, outs = stubify(((out,), {}))
@@ -678,8 +714,8 @@ class ExecutionServer:
             if req.grad_enabled:
                 self.records[req.call_id] = ExecRecord(req.mb, leaves, outs, src, req.prev_hop)
             if req.chain:
-                self.comm.server_send(ForwardRequest(req.mb, req.call_id, (name, nxt_span), skel, req.grad_enabled,
-                                                     req.requester, rest, self.me), nxt)
+                self.comm.server_send(ForwardRequest(req.mb, req.call_id, (name, nxt_span, ckpt), skel, req.grad_enabled,
+                                                     req.requester, rest, self.me, req.autocast), nxt)
                 self.p2p.send(outs, nxt)
             else:
                 self.comm.server_send(ForwardResult(req.mb, req.call_id, skel), req.requester)

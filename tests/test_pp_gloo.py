@@ -480,3 +480,120 @@ def test_host_bus_fallback_for_pipeline_tensors(monkeypatch):
     for r in host + host_static:
         assert r["host"]["sent"] > 0 and r["host"]["received"] > 0 and r["host"]["bytes"] > 0
     assert host_static[0]["stats"]["replayed_steps"] == 4
+
+
+def _seq_ckpt_worker(rank, world, configured):
+    import copy
+
+    import torch.nn as nn
+
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": False, "auto_partition": False,
+              "default_partition": 0})
+    torch.manual_seed(1)
+    calls = {"n": 0}
+
+    class Block(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.lin = nn.Linear(16, 16)
+
+        def forward(self, x):
+            calls["n"] += 1
+            return torch.tanh(self.lin(x))
+
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.inp = nn.Linear(8, 16)
+            self.seq = nn.Sequential(*[Block() for _ in range(4)])
+            self.out = nn.Linear(16, 2)
+
+        def forward(self, x):
+            h = self.inp(x)
+            h = self.seq(h) if configured else smp.checkpoint_sequential(self.seq, h, strategy="group_2")
+            return self.out(h)
+
+    net = Net()
+    oracle = copy.deepcopy(net)
+    for i, layer in enumerate(net.seq):
+        smp.set_partition(layer, 0 if i < 2 else 1)
+    if configured:
+        smp.set_activation_checkpointing(net.seq, strategy="each")
+    model = smp.DistributedModel(net)
+
+    @smp.step
+    def step(model, x):
+        loss = model(x).pow(2).mean()
+        model.backward(loss)
+        return loss
+
+    x = torch.randn(4, 8, generator=torch.Generator().manual_seed(2))
+    loss = step(model, x).reduce_mean().item()
+    mine = calls["n"]
+    ol = oracle(x).pow(2).mean() if configured else None
+    if ol is None:
+        h = oracle.inp(x)
+        for blk in oracle.seq:
+            h = blk(h)
+        ol = oracle.out(h).pow(2).mean()
+    ol.backward()
+    ref = dict(oracle.named_parameters())
+    worst = max((p.grad - ref[n].grad).abs().max().item() for n, p in model.local_named_parameters())
+    return {"loss": loss, "oracle": ol.item(), "worst": worst, "calls": mine}
+
+
+@pytest.mark.parametrize("configured", [False, True])
+def test_checkpointed_sequential_spanning_two_stages(configured):
+    """An ``nn.Sequential`` cut across two pipeline ranks, checkpointed through ``smp.checkpoint_sequential`` or
+    ``smp.set_activation_checkpointing``: each rank checkpoints its own run of layers (every local layer runs twice
+    per microbatch: forward and recomputation), results match the plain model."""
+    res = run_distributed(_seq_ckpt_worker, 2, configured, timeout=240)
+    for r in res:
+        assert abs(r["loss"] - r["oracle"]) < 1e-6 and r["worst"] < 1e-6, r
+        assert r["calls"] == 2 * 2 * 2, r          # 2 local layers x 2 microbatches x (forward + recompute)
+
+
+def _amp_worker(rank, world):
+    import torch.nn as nn
+
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": False})
+    torch.manual_seed(1)
+    net = nn.Sequential(nn.Linear(8, 16), nn.Tanh(), nn.Linear(16, 16), nn.Tanh(), nn.Linear(16, 2))
+    model = smp.DistributedModel(net)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+    scaler = smp.amp.GradScaler(init_scale=2.0 ** 8, growth_interval=2)
+    seen = []
+    for m in net:
+        if isinstance(m, nn.Linear):
+            m.register_forward_hook(lambda mod, a, out: seen.append(out.dtype))
+
+    @smp.step
+    def step(model, x):
+        with torch.autocast("cpu", dtype=torch.bfloat16):
+            loss = model(x).float().pow(2).mean()
+        model.backward(scaler.scale(loss))
+        return loss
+
+    out = []
+    for i in range(3):
+        x = torch.randn(4, 8, generator=torch.Generator().manual_seed(2 + i))
+        opt.zero_grad()
+        out.append(step(model, x).reduce_mean().item())
+        scaler.step(opt)
+        scaler.update()
+    return {"losses": out, "scale": scaler.get_scale(), "dtypes": sorted({str(d) for d in seen}),
+            "n_local": len(list(model.local_parameters()))}
+
+
+def test_autocast_and_grad_scaler_across_pipeline_stages():
+    """The caller's autocast region covers modules executed on other stages; ``smp.amp.GradScaler`` works on stages
+    that never ran the step function (they start from the same scale) and all stages agree on the scale."""
+    res = run_distributed(_amp_worker, 2, timeout=240)
+    assert res[0]["losses"] == res[1]["losses"] and res[0]["losses"][-1] < res[0]["losses"][0]
+    assert res[0]["scale"] == res[1]["scale"] == 2.0 ** 9          # grew once after two clean steps
+    for r in res:
+        assert r["n_local"] > 0 and r["dtypes"] == ["torch.bfloat16"], r
