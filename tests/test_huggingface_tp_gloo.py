@@ -69,3 +69,47 @@ def test_hf_model_under_tp2(family):
     assert abs(mean - res[0]["ref"]) < 2e-5, (mean, res[0]["ref"])
     for r in res:
         assert r["worst"] == 0.0 and not r["missing"], (r["worst"], r["missing"][:4])
+
+
+def _hf_pp_worker(rank, world):
+    import copy
+
+    import smdistributed_modelparallel_b200 as smp
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": False})
+    torch.manual_seed(1)
+    cfg = GPT2Config(n_layer=4, n_head=4, n_embd=32, vocab_size=64, n_positions=16, resid_pdrop=0.0, embd_pdrop=0.0,
+                     attn_pdrop=0.0)
+    net = GPT2LMHeadModel(cfg)
+    oracle = copy.deepcopy(net)
+    model = smp.DistributedModel(net)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+
+    @smp.step
+    def step(model, ids):
+        out = model(input_ids=ids, labels=ids)            # keyword arguments, ModelOutput result
+        model.backward(out.loss)
+        return out.loss
+
+    ids = torch.randint(0, 64, (4, 16), generator=torch.Generator().manual_seed(3))
+    opt.zero_grad()
+    loss = step(model, ids).reduce_mean().item()
+    ol = sum(oracle(input_ids=ids[i:i + 2], labels=ids[i:i + 2]).loss / 2 for i in (0, 2))
+    ol.backward()
+    ref = dict(oracle.named_parameters())
+    worst = max((p.grad - ref[n].grad).abs().max().item() for n, p in model.local_named_parameters())
+    opt.step()
+    loss2 = step(model, ids).reduce_mean().item()
+    return {"loss": loss, "oracle": ol.item(), "worst": worst, "loss2": loss2,
+            "ranks": sorted(set(smp.state.module_manager.partition_info().values()))}
+
+
+def test_stock_hf_gpt2_under_pp2():
+    """An unmodified HuggingFace GPT-2 (keyword arguments, ``ModelOutput`` results, tied embeddings) split over two
+    pipeline stages by the auto-partitioner: loss and local gradients match the single-process model."""
+    res = run_distributed(_hf_pp_worker, 2, timeout=300)
+    for r in res:
+        assert r["ranks"] == [0, 1]
+        assert abs(r["loss"] - r["oracle"]) < 1e-5 and r["worst"] < 1e-5, r
+        assert r["loss2"] < r["loss"]
