@@ -35,7 +35,7 @@ from ..backend.exceptions import SMPValidationError, UnsupportedShardedConfigErr
 from ..backend.logger import get_logger
 from ..ops import multi_tensor as MT
 from ..precision.loss_scaler import DynamicLossScaler, LossScaler
-from .boundary import mark_inputs
+from .boundary import map_tensors, mark_inputs
 from .grad_buffer import GradBuffer
 
 
@@ -237,9 +237,23 @@ class ShardedDataParallelEngine:
         by_module = OrderedDict()
         for u in self.units:
             by_module.setdefault(u.module, []).append(u)
+        # A parameter shared with a module outside its unit's subtree (tied input / output embeddings of a stock
+        # HuggingFace model): that module gathers and releases the unit around its own forward / backward as well,
+        # like a second use of the unit's module.
+        hooked = {}
+        for u in self.units:
+            hooked.setdefault(u, set()).add(names[u.module])
+        for m in root.modules():
+            mn = names[m]
+            for q in m.parameters(recurse=False):
+                u = getattr(q, "_smp_sdp_unit", None)
+                if u is None or any(h == "" or mn == h or mn.startswith(h + ".") for h in hooked[u]):
+                    continue
+                by_module.setdefault(m, []).append(u)
+                hooked[u].add(mn)
         for m, us in by_module.items():
             self._hooks.append(m.register_forward_pre_hook(lambda mod, a, _us=us: self._pre_forward(_us, a)))
-            self._hooks.append(m.register_forward_hook(lambda mod, a, out, _us=us: self._post_forward(_us)))
+            self._hooks.append(m.register_forward_hook(lambda mod, a, out, _us=us: self._post_forward(_us, out)))
             self._hooks.append(m.register_full_backward_pre_hook(lambda mod, g, _us=us: self._pre_backward(_us)))
             self._hooks.append(m.register_full_backward_hook(lambda mod, gi, go, _us=us: self._post_backward(_us, gi)))
         if self.persistent:
@@ -347,7 +361,16 @@ class ShardedDataParallelEngine:
         # units are flushed at the end of backward)
         return mark_inputs(args, lambda _us=tuple(units): [self._reduce_unit(u) for u in _us])
 
-    def _post_forward(self, units):
+    def _post_forward(self, units, out=None):
+        if out is not None and torch.is_grad_enabled() and not self._in_backward:
+            # module backward-pre hooks only see plain tensor / tuple outputs: for anything else (a dict, a
+            # HuggingFace ModelOutput) the unit is gathered when the first gradient of an output tensor arrives
+            if not (torch.is_tensor(out) or (isinstance(out, tuple) and all(torch.is_tensor(o) for o in out))):
+                def arm(t, _us=tuple(units)):
+                    if t.requires_grad:
+                        t.register_hook(lambda g, _us=_us: self._pre_backward(_us))
+                    return t
+                map_tensors(out, arm)
         for u in units:
             u.users -= 1
             if u.users <= 0 and u.full_grad is None:

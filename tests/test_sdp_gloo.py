@@ -290,3 +290,52 @@ def test_sdp_resume_with_parameter_groups_and_sharded_initialisation():
     for r in res:
         assert r["want"] == r["got"], r
         assert r["decay"] == [0.1, 0.0] and all(n > 0 for n in r["groups"])
+
+
+def _hf_sdp_worker(rank, world, unit_elements):
+    import copy
+
+    import smdistributed_modelparallel_b200 as smp
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    os.environ["SMP_SDP_UNIT_ELEMENTS"] = str(unit_elements)
+    smp.init({"sharded_data_parallel_degree": 2, "microbatches": 2, "ddp": True,
+              "sdp_param_persistence_threshold": 100, "sdp_gradient_clipping": 0.0})
+    torch.manual_seed(1)
+    cfg = GPT2Config(n_layer=2, n_head=4, n_embd=32, vocab_size=64, n_positions=16, resid_pdrop=0.0, embd_pdrop=0.0,
+                     attn_pdrop=0.0)
+    net = GPT2LMHeadModel(cfg)
+    oracle = copy.deepcopy(net)
+    model = smp.DistributedModel(net)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+    oopt = torch.optim.SGD(oracle.parameters(), lr=0.1)
+
+    @smp.step
+    def step(model, ids):
+        out = model(input_ids=ids, labels=ids)
+        model.backward(out.loss)
+        return out.loss
+
+    g = torch.Generator().manual_seed(3)
+    for _ in range(2):
+        ids = torch.randint(0, 64, (8, 16), generator=g)
+        opt.zero_grad()
+        step(model, ids[rank * 4:(rank + 1) * 4])
+        opt.step()
+        oopt.zero_grad()
+        sum(oracle(input_ids=ids[i:i + 2], labels=ids[i:i + 2]).loss / 4 for i in (0, 2, 4, 6)).backward()
+        oopt.step()
+    full, osd = model.state_dict(), oracle.state_dict()
+    return {"worst": max((full[k].float() - osd[k]).abs().max().item() for k in osd if k in full),
+            "units": len(model.sdp_engine.units)}
+
+
+@pytest.mark.parametrize("unit_elements,min_units", [(5000, 4), (10 ** 9, 1)])
+def test_stock_hf_gpt2_with_tied_embeddings_under_sdp(unit_elements, min_units):
+    """A stock HuggingFace GPT-2 under sharded data parallelism.  Small units: the output projection shares its
+    weight with the input embedding, whose unit it therefore gathers / reduces too.  One unit for the whole model:
+    its module takes keyword arguments and returns a ``ModelOutput``, so the unit is re-gathered for backward from
+    hooks on the output tensors.  Parameters track the single-process model either way."""
+    res = run_distributed(_hf_sdp_worker, 2, unit_elements, timeout=300)
+    for r in res:
+        assert r["units"] >= min_units and r["worst"] < 1e-5, r
