@@ -597,3 +597,49 @@ def test_autocast_and_grad_scaler_across_pipeline_stages():
     assert res[0]["scale"] == res[1]["scale"] == 2.0 ** 9          # grew once after two clean steps
     for r in res:
         assert r["n_local"] > 0 and r["dtypes"] == ["torch.bfloat16"], r
+
+
+def _failing_stage_worker(rank, world):
+    import torch.nn as nn
+
+    import smdistributed_modelparallel_b200 as smp
+
+    class Boom(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.lin = nn.Linear(8, 8)
+            self.fail = False
+
+        def forward(self, x):
+            if self.fail:
+                raise ValueError("deliberate failure on the second stage")
+            return self.lin(x)
+
+    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": False, "auto_partition": False,
+              "default_partition": 0})
+    net = nn.Sequential(nn.Linear(8, 8), Boom(), nn.Linear(8, 2))
+    smp.set_partition(net[1], 1)
+    model = smp.DistributedModel(net)
+
+    @smp.step
+    def step(model, x):
+        loss = model(x).pow(2).mean()
+        model.backward(loss)
+        return loss
+
+    x = torch.randn(4, 8)
+    step(model, x)
+    net[1].fail = True
+    try:
+        step(model, x)
+    except Exception as e:   # noqa: BLE001
+        return f"{type(e).__name__}: {e}"
+    return None
+
+
+def test_failure_inside_a_remote_module_fails_both_stages():
+    """A module raising on the second stage: that stage re-raises its own exception, the leader gets it back as
+    the failure of the remote call (with the remote traceback); nobody hangs."""
+    res = run_distributed(_failing_stage_worker, 2, timeout=180)
+    assert res[0].startswith("SMPRuntimeError") and "deliberate failure on the second stage" in res[0]
+    assert res[1].startswith("ValueError: deliberate failure")
