@@ -643,3 +643,41 @@ def test_failure_inside_a_remote_module_fails_both_stages():
     res = run_distributed(_failing_stage_worker, 2, timeout=180)
     assert res[0].startswith("SMPRuntimeError") and "deliberate failure on the second stage" in res[0]
     assert res[1].startswith("ValueError: deliberate failure")
+
+
+def _reinit_worker(rank, world):
+    import smdistributed_modelparallel_b200 as smp
+
+    res = []
+    for conf in ({"tensor_parallel_degree": 2}, {"pipeline_parallel_degree": 2},
+                 {"tensor_parallel_degree": 2, "pipeline_parallel_degree": 2}):
+        smp.init(dict(conf, microbatches=2, ddp=True, ddp_dist_backend="gloo"))
+        torch.manual_seed(1)
+        with smp.model_creation(tensor_parallelism=smp.tp_size() > 1):
+            module = smp.nn.DistributedTransformerLMHead(**CFG)
+        model = smp.DistributedModel(module)
+        opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+
+        @smp.step
+        def step(model, ids):
+            loss, _ = model((ids, None, None, None, ids))
+            model.backward(loss)
+            return loss
+
+        ids = torch.randint(0, CFG["vocab_size"], (4, 16), generator=torch.Generator().manual_seed(3))
+        opt.zero_grad()
+        first = step(model, ids).reduce_mean().item()
+        opt.step()
+        second = step(model, ids).reduce_mean().item()
+        res.append((smp.pp_size(), smp.tp_size(), smp.dp_size(), first, second))
+    return res
+
+
+def test_reinitialising_with_other_degrees_in_one_process():
+    """``smp.init`` again with another layout (tp2 -> pp2 -> pp2 x tp2 on the same four processes): groups, engine
+    and partition are rebuilt each time and training works in each."""
+    res = run_distributed(_reinit_worker, 4, timeout=300)
+    for r in res:
+        assert [x[:3] for x in r] == [(1, 2, 4), (2, 1, 2), (2, 2, 2)]
+        assert all(second < first for *_, first, second in r)
+    assert res[0][0][3] == res[0][2][3]            # the same tensor-parallel model whether or not it is pipelined
