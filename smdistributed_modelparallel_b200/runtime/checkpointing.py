@@ -124,8 +124,38 @@ class CheckpointFunction(torch.autograd.Function):
         return (None, None, None, None, *in_grads)
 
 
+_warned_cache = False
+
+
+def _is_kv_cache(v):
+    return hasattr(v, "update") and hasattr(v, "get_seq_length") and not torch.is_tensor(v)
+
+
+def _drop_stateful_caches(kwargs, args=()):
+    """A key/value cache object (HuggingFace ``Cache``: ``update`` + ``get_seq_length``) handed to a checkpointed
+    module is appended to by the forward pass and *again* by the recomputation, which then attends over doubled
+    keys and produces wrong gradients.  Training needs no cache: it is dropped (as HuggingFace's own gradient
+    checkpointing does with ``use_cache``), with one warning."""
+    global _warned_cache
+    out = None
+    for k, v in kwargs.items():
+        if _is_kv_cache(v) or (k == "use_cache" and v is True):
+            if out is None:
+                out = dict(kwargs)
+            out[k] = False if k == "use_cache" else None
+    new_args = tuple(None if _is_kv_cache(a) else a for a in args) if any(_is_kv_cache(a) for a in args) else args
+    if (out is not None or new_args is not args) and not _warned_cache:
+        _warned_cache = True
+        from ..backend.logger import get_logger
+        get_logger().warning("activation checkpointing: key/value caches passed to a checkpointed module are "
+                             "dropped (a cache mutated by the recomputation corrupts gradients); pass use_cache=False")
+    return new_args, (kwargs if out is None else out)
+
+
 def checkpoint(module_or_fn, *args, preserve_rng_state: bool = True, **kwargs):
     """Checkpoint one call of a module (or function): activations inside are recomputed in backward."""
+    if torch.is_grad_enabled():
+        args, kwargs = _drop_stateful_caches(kwargs, args)
     tensors = []
     skel = _flatten((args, kwargs), tensors)
     if not any(t.requires_grad for t in tensors) and not any(

@@ -120,3 +120,37 @@ def test_set_activation_checkpointing_through_distributed_model():
     ref_net(x).square().mean().backward()                    # mean over the batch = mean of the microbatch means
     for a, b in zip(ref_net.parameters(), model.module.parameters()):
         assert torch.allclose(a.grad, b.grad, atol=1e-6)
+
+
+def test_checkpointed_hf_blocks_ignore_the_kv_cache():
+    """A stock HuggingFace GPT-2 hands every block a mutable key/value cache (``use_cache`` defaults to true); the
+    recomputation would append to it a second time and attend over doubled keys.  Checkpointed calls drop the cache,
+    so gradients equal those of the plain model."""
+    import copy
+
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    smp.reset()
+    smp.init({"microbatches": 2})
+    torch.manual_seed(1)
+    cfg = GPT2Config(n_layer=2, n_head=4, n_embd=32, vocab_size=64, n_positions=16, resid_pdrop=0.0, embd_pdrop=0.0,
+                     attn_pdrop=0.0)
+    net = GPT2LMHeadModel(cfg)
+    oracle = copy.deepcopy(net)
+    for blk in net.transformer.h:
+        smp.set_activation_checkpointing(blk)
+    model = smp.DistributedModel(net)
+
+    @smp.step
+    def step(model, ids):
+        out = model(input_ids=ids, labels=ids)             # use_cache left at its default
+        model.backward(out.loss)
+        return out.loss
+
+    ids = torch.randint(0, 64, (4, 16), generator=torch.Generator().manual_seed(3))
+    loss = step(model, ids).reduce_mean().item()
+    ol = sum(oracle(input_ids=ids[i:i + 2], labels=ids[i:i + 2]).loss / 2 for i in (0, 2))
+    ol.backward()
+    ref = dict(oracle.named_parameters())
+    worst = max((p.grad - ref[n].grad).abs().max().item() for n, p in net.named_parameters())
+    assert abs(loss - ol.item()) < 1e-6 and worst < 1e-6, (loss, ol.item(), worst)
