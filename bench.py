@@ -273,9 +273,10 @@ def main():
     if tp > 1:
         conf["prescaled_batch"] = False
     os.environ.setdefault("SMP_LOG_LEVEL", "warning")
+    if baseline or os.environ.get("BENCH_TP_COMM") == "nccl":
+        conf["fused_tp_collectives"] = False       # NCCL collectives next to the GEMMs (the comparison arm)
     smp.init(conf)
     from smdistributed_modelparallel_b200.parallel import tp_ops
-    tp_ops.set_comm_mode("nccl" if (baseline or os.environ.get("BENCH_TP_COMM") == "nccl") else "fused")
     dev = torch.device("cuda", smp.local_rank())
     torch.manual_seed(1234 + smp.rank())
 

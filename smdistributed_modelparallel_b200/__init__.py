@@ -69,6 +69,12 @@ def init(config=None):
                           "running the same kernels as optimize='speed'")
     if torch.cuda.is_available():
         torch.cuda.set_device(core.local_rank())
+    # tensor-parallel collectives: the fused peer-memory kernels are the default path on GPUs (they still check
+    # per call that the group sits on one NVSwitch domain and that the shapes tile); `fused_tp_collectives: false`
+    # or SMP_TP_COMM=nccl selects the NCCL + GEMM composition (the measured baseline)
+    from .parallel import tp_ops
+
+    tp_ops.set_comm_mode(tp_ops.select_comm_mode(cfg, torch.cuda.is_available()))
     if core.rank() == 0:
         cfg.display_config()
 

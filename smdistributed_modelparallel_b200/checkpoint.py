@@ -1,9 +1,12 @@
 """Checkpoint API: ``smp.save`` / ``smp.load`` / ``smp.save_checkpoint`` / ``smp.resume_from_checkpoint``.
 
-On-disk layout and key names are the reference's, so checkpoints written by either library can be
-read by the other (reference smdistributed/modelparallel/torch/checkpoint.py:42-121 file-name schemes,
-:124-165 save/load, :180-297 save_checkpoint, :300-319 sharded-DP files, :381-484 resume, :487-536
-config verification):
+On-disk layout and key names are the reference's (reference smdistributed/modelparallel/torch/checkpoint.py:
+42-121 file-name schemes, :124-165 save/load, :180-297 save_checkpoint, :300-319 sharded-DP files, :381-484
+resume, :487-536 config verification).  Model, optimizer and fp16-state files of the pipeline / tensor / data
+parallel modes use the reference's keys and pickle the loss scaler under the reference's class path, so they can
+be exchanged with it (``tests/test_checkpoint_api.py::test_reference_shaped_fp16_states``); the sharded-data-
+parallel optimizer files keep the reference's names but hold this engine's own state (the reference's are
+DeepSpeed dictionaries) and are not interchangeable:
 
     {path}/{tag}_partial/model_{pp}_{tp}.pt                    local state dict of (pp, tp), rdp_rank 0
     {path}/{tag}_partial/optimizer_states_{pp}_{tp}[_{rdp}].pt  (+ _{rdp} with shard_optimizer_state)

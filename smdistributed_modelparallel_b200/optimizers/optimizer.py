@@ -206,7 +206,8 @@ class DistributedOptimizer:
             return None
         b = self._bit16
         return {
-            "loss_scaler": b.loss_scaler.state_dict(),
+            # the scaler object itself, as the reference writes it (reference optimizers/optimizer.py:185-190)
+            "loss_scaler": b.loss_scaler.for_checkpoint(),
             "dynamic_loss_scale": b.dynamic_loss_scale,
             "overflow": b.overflow,
             "first_closure_call_this_step": b.first_closure_call_this_step,

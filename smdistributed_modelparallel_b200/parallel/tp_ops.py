@@ -36,6 +36,15 @@ def get_comm_mode() -> str:
     return _comm_mode
 
 
+def select_comm_mode(cfg, cuda_available: bool) -> str:
+    """The mode ``smp.init`` installs: 'fused' unless the config key ``fused_tp_collectives`` is false, the
+    environment says ``SMP_TP_COMM=nccl`` or there is no CUDA device."""
+    import os
+
+    want = bool(getattr(cfg, "fused_tp_collectives", True)) and os.environ.get("SMP_TP_COMM", "fused") != "nccl"
+    return "fused" if (want and cuda_available) else "nccl"
+
+
 def _group_size(group) -> int:
     return 1 if group is None else dist.get_world_size(group)
 

@@ -183,3 +183,66 @@ def test_bf16_masters_survive_a_resume():
         smp.resume_from_checkpoint(d, tag="b")
         got = run(model2, opt2, step2, 3, 2)
         assert want == got, (want, got)
+
+
+def test_reference_shaped_fp16_states():
+    """fp16_states files carry the loss scaler as a pickled OBJECT whose class resolves under
+    smdistributed.modelparallel.torch.fp16.loss_scaler (reference torch/optimizers/optimizer.py:185-190,270-271).
+    A file shaped like the reference's loads here, and what this library writes has the same shape."""
+    import pickle
+
+    from smdistributed.modelparallel.torch.fp16.loss_scaler import DynamicLossScaler as RefPathScaler
+
+    with tempfile.TemporaryDirectory() as d:
+        smp.reset()
+        smp.init({"microbatches": 1, "fp16": True})
+        torch.manual_seed(0)
+        with smp.model_creation(dtype=torch.float16):
+            net = nn.Sequential(nn.Linear(8, 8), nn.Tanh(), nn.Linear(8, 4))
+        model = smp.DistributedModel(net)
+        opt = smp.DistributedOptimizer(torch.optim.Adam(model.parameters(), lr=1e-3), dynamic_loss_scale=True)
+
+        @smp.step
+        def train_step(model, x):
+            loss = model(x).float().pow(2).mean()
+            model.backward(loss)
+            return loss
+
+        opt.zero_grad()
+        train_step(model, torch.randn(2, 8).half())
+        opt.step()
+
+        # (1) what this library writes: an object at the reference's class path with the reference's fields
+        mine = opt.local_fp16_state_dict()
+        ls = mine["loss_scaler"]
+        assert type(ls).__module__ == "smdistributed.modelparallel.torch.fp16.loss_scaler"
+        assert type(ls).__name__ == "DynamicLossScaler" and ls.model is None
+        for field in ("cur_scale", "cur_iter", "last_overflow_iter", "scale_factor", "scale_window", "min_scale",
+                      "delayed_shift", "cur_hysteresis", "consecutive_hysteresis"):
+            assert hasattr(ls, field), field
+        assert set(mine) == {"loss_scaler", "dynamic_loss_scale", "overflow", "first_closure_call_this_step",
+                             "fp32_from_fp16"}
+        pickle.loads(pickle.dumps(mine))
+
+        # (2) a file shaped like the reference's: the object is built field by field the way the reference's
+        # constructor leaves it (no `dynamic` attribute, a `model` slot), saved with torch.save
+        ref_obj = RefPathScaler.__new__(RefPathScaler)
+        ref_obj.__dict__.update(cur_scale=2.0 ** 14, cur_iter=37, last_overflow_iter=30, scale_factor=2.0,
+                                scale_window=1000, min_scale=1, delayed_shift=2, cur_hysteresis=1,
+                                consecutive_hysteresis=False, model=None)
+        masters = [[m.detach().cpu().clone() + 0.25 for m in grp] for grp in opt.fp16_optimizer.fp32_from_fp16_groups]
+        path = os.path.join(d, "fp16_states_0_0.pt")
+        torch.save({"loss_scaler": ref_obj, "dynamic_loss_scale": True, "overflow": False,
+                    "first_closure_call_this_step": True, "fp32_from_fp16": masters}, path)
+        loaded = torch.load(path, weights_only=False)
+        opt.load_optimizer_checkpoint_state({"optimizer_state_dict": opt.optimizer.state_dict(), "fp16": loaded})
+        b = opt.fp16_optimizer
+        assert b.loss_scaler.cur_scale == 2.0 ** 14 and b.loss_scaler.cur_iter == 37
+        assert b.loss_scaler.cur_hysteresis == 1 and b.loss_scaler.delayed_shift == 2
+        assert b.loss_scaler.dynamic is True                      # own field survives a reference-shaped load
+        for cur, saved in zip(b.fp32_from_fp16_groups, masters):
+            for c, s in zip(cur, saved):
+                assert torch.equal(c.detach().cpu(), s)
+        # the older dict form still loads
+        b.loss_scaler.load_state_dict({"cur_scale": 8.0})
+        assert b.loss_scaler.cur_scale == 8.0

@@ -104,3 +104,26 @@ def test_foreign_data_parallel_backends_are_refused(key):
 
     with pytest.raises(SMPUnsupportedError, match="ddp"):
         smp.init({key: True})
+
+
+def test_fused_tp_collectives_key_selects_the_comm_mode(monkeypatch):
+    """`fused_tp_collectives` (default true) is what picks the peer-memory kernels over NCCL around the
+    tensor-parallel GEMMs; without a CUDA device the mode is 'nccl' whatever the key says."""
+    import torch
+
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200.parallel import tp_ops
+
+    monkeypatch.delenv("SMP_TP_COMM", raising=False)
+    on, off = ModelParallelConfig({}), ModelParallelConfig({"fused_tp_collectives": False})
+    assert tp_ops.select_comm_mode(on, True) == "fused" and tp_ops.select_comm_mode(off, True) == "nccl"
+    assert tp_ops.select_comm_mode(on, False) == "nccl"
+    monkeypatch.setenv("SMP_TP_COMM", "nccl")
+    assert tp_ops.select_comm_mode(on, True) == "nccl"
+    monkeypatch.delenv("SMP_TP_COMM")
+    # smp.init installs the selected mode
+    tp_ops.set_comm_mode("fused")
+    smp.init({"microbatches": 1, "fused_tp_collectives": False})
+    assert tp_ops.get_comm_mode() == "nccl"
+    smp.init({"microbatches": 1})
+    assert tp_ops.get_comm_mode() == ("fused" if torch.cuda.is_available() else "nccl")
