@@ -232,8 +232,8 @@ class DistributedAttentionLayer(DistributedModule):
                 gemm_scale /= float(self.layer_idx + 1)
         ctx = A.core_attention(q, k, v, causal=causal, mask=mask, scale=scale, dropout_p=self.attention_dropout_prob,
                                training=self.training, window=self.window_size if causal else None,
-                               gemm_scale=gemm_scale)
-        return A.heads_to_tokens(ctx).reshape(B * S, la)
+                               gemm_scale=gemm_scale, token_major=True)
+        return ctx.reshape(B * S, la)        # [B, S, heads, d] straight from the attention kernel
 
     def forward(self, inp):
         """inp: (hidden [b, S, H], attention_mask) or (hidden, cross_states, attention_mask)."""

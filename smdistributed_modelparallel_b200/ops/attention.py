@@ -1,11 +1,13 @@
-"""Attention building blocks on the sm_100a kernels: autograd batched GEMMs (tcgen05), QKV split with
-fused rotary embedding, head transposes and the composed core attention.
+"""Attention building blocks on the sm_100a kernels: the flash-style fused attention (forward and backward,
+``csrc/kernels/sm100/attention.cu``), QKV split with fused rotary embedding and head transposes.
 
-The reference computes attention as ``baddbmm`` -> fused softmax -> dropout -> ``matmul`` (reference
-smdistributed/modelparallel/torch/nn/transformer.py:1617-1657,1769-1835) and rotary embeddings with
-eager ops (:114-163,1565-1615).  Here both batched GEMMs run on the tcgen05 kernel in the layouts the
-data already has (no transposed copies), the softmax is the native causal/masked kernel and rotary is
-fused into the QKV split.
+The reference computes attention as ``baddbmm`` -> fused softmax -> dropout -> ``matmul`` and keeps the
+``[B, heads, Sq, Sk]`` scores and probabilities for backward (reference smdistributed/modelparallel/torch/nn/
+transformer.py:1617-1657,1769-1835), and rotary embeddings with eager ops (:114-163,1565-1615).  Here one kernel
+per direction keeps the score tiles in tensor memory: nothing of size ``Sq x Sk`` is ever written to global memory,
+the backward pass recomputes the probabilities from the saved log-sum-exp rows, and causal / byte / local-window
+masks and dropout (counter-based, so a checkpoint recomputation sees the same mask) are applied in registers.
+Rotary is fused into the QKV split.
 """
 
 from __future__ import annotations
@@ -15,51 +17,6 @@ import math
 import torch
 
 from . import _native as N
-from .gemm import gemm
-from .softmax import scaled_masked_softmax, scaled_upper_triang_masked_softmax
-
-
-class _BmmNT(torch.autograd.Function):
-    """out[b] = alpha * a[b] @ b[b]^T   (a [B,M,K], b [B,N,K])."""
-
-    @staticmethod
-    def forward(ctx, a, b, alpha):
-        ctx.alpha = alpha
-        ctx.save_for_backward(a, b)
-        return gemm(a, b, alpha=alpha)
-
-    @staticmethod
-    def backward(ctx, dout):
-        a, b = ctx.saved_tensors
-        dout = dout.contiguous()
-        da = gemm(dout, b, b_mn_major=True, alpha=ctx.alpha) if ctx.needs_input_grad[0] else None
-        db = gemm(dout, a, a_mn_major=True, b_mn_major=True, alpha=ctx.alpha) if ctx.needs_input_grad[1] else None
-        return da, db, None
-
-
-class _BmmNN(torch.autograd.Function):
-    """out[b] = a[b] @ b[b]   (a [B,M,K], b [B,K,N])."""
-
-    @staticmethod
-    def forward(ctx, a, b):
-        ctx.save_for_backward(a, b)
-        return gemm(a, b, b_mn_major=True)
-
-    @staticmethod
-    def backward(ctx, dout):
-        a, b = ctx.saved_tensors
-        dout = dout.contiguous()
-        da = gemm(dout, b) if ctx.needs_input_grad[0] else None
-        db = gemm(a, dout, a_mn_major=True, b_mn_major=True) if ctx.needs_input_grad[1] else None
-        return da, db
-
-
-def bmm_nt(a, b, alpha: float = 1.0):
-    return _BmmNT.apply(a.contiguous(), b.contiguous(), alpha)
-
-
-def bmm_nn(a, b):
-    return _BmmNN.apply(a.contiguous(), b.contiguous())
 
 
 # ----------------------------------------------------------------------------------------- rotary
@@ -184,92 +141,123 @@ def tokens_to_heads(x, heads):
     return _HeadTranspose.apply(x.reshape(B, S, heads, hd // heads), True)
 
 
-class _CausalAttention(torch.autograd.Function):
-    """softmax(scale q k^T + causal mask) v with every GEMM told about the triangle: score tiles above the
-    diagonal are never computed or written, and the products with P / dS (lower triangular) only reduce over the
-    non-zero part - about 44 % of the attention FLOPs and score traffic at S = 2048."""
+def _operand(t):
+    """TMA needs a unit inner stride, 16-byte aligned outer strides and base; copy only when a view breaks that."""
+    if t.stride(-1) != 1 or any(st % 8 for st in t.stride()[:-1]) or t.data_ptr() % 16:
+        return t.contiguous()
+    return t
+
+
+def _mask_args(mask):
+    if mask is None:
+        return None, 0, 0, 0
+    return (mask.data_ptr(), mask.stride(0) if mask.shape[0] > 1 else 0, mask.stride(1) if mask.shape[1] > 1 else 0,
+            mask.stride(2) if mask.shape[2] > 1 else 0)
+
+
+class _FlashAttention(torch.autograd.Function):
+    """softmax(scale q k^T + masks) v on the fused tcgen05 kernels.  q, k, v are [B, heads, S, d] views; the context
+    comes back either in the same layout or token-major ([B, Sq, heads, d]) so the output projection can consume it
+    without a transpose.  Saved for backward: q, k, v, the context and one fp32 log-sum-exp per row."""
 
     @staticmethod
-    def forward(ctx, q, k, v, scale, gemm_scale=1.0):
-        from .gemm import gemm
-
-        BH, S, d = q.shape
-        scores = torch.empty(BH, S, S, dtype=q.dtype, device=q.device)
-        gemm(q, k, out=scores, causal="lower_out", alpha=gemm_scale)    # stored scores = gemm_scale * q k^T
-        probs = torch.empty_like(scores)
+    def forward(ctx, q, k, v, mask, scale, causal, window, p_drop, seed, offset, token_major):
+        B, h, Sq, d = q.shape
+        Sk = k.shape[2]
+        q, k, v = _operand(q), _operand(k), _operand(v)
+        if token_major:
+            o = torch.empty(B, Sq, h, d, dtype=q.dtype, device=q.device)
+            o_str = (o.stride(0), o.stride(2), o.stride(1))
+        else:
+            o = torch.empty(B, h, Sq, d, dtype=q.dtype, device=q.device)
+            o_str = (o.stride(0), o.stride(1), o.stride(2))
+        lse = torch.empty(B * h, Sq, dtype=torch.float32, device=q.device)
         N.count_launch()
-        N.call("smpk_softmax_fwd", N.stream_ptr(q.device), scores.data_ptr(), probs.data_ptr(), N.dtype_code(q.dtype),
-               None, 3, float(scale), BH, 1, S, S)       # mode 3: causal, zero fill only up to the next 256 columns
-        del scores
-        out = gemm(probs, v, b_mn_major=True, causal="lower_a")
-        ctx.save_for_backward(q, k, v, probs)
-        ctx.scale, ctx.gemm_scale = scale, gemm_scale
-        return out
+        N.call("smpk_attn_fwd", N.stream_ptr(q.device), N.dtype_code(q.dtype), B, h, Sq, Sk, d,
+               q.data_ptr(), *q.stride()[:3], k.data_ptr(), *k.stride()[:3], v.data_ptr(), *v.stride()[:3],
+               o.data_ptr(), *o_str, lse.data_ptr(), float(scale), int(causal), int(window), *_mask_args(mask),
+               float(p_drop), int(seed), int(offset))
+        ctx.save_for_backward(q, k, v, o, lse, mask)
+        ctx.meta = (float(scale), int(causal), int(window), float(p_drop), int(seed), int(offset), token_major)
+        return o
 
     @staticmethod
-    def backward(ctx, dout):
-        from .gemm import gemm
+    def backward(ctx, do):
+        q, k, v, o, lse, mask = ctx.saved_tensors
+        scale, causal, window, p_drop, seed, offset, token_major = ctx.meta
+        B, h, Sq, d = q.shape
+        Sk = k.shape[2]
+        do = _operand(do)
+        if token_major:
+            o_str = (o.stride(0), o.stride(2), o.stride(1))
+            g_str = (do.stride(0), do.stride(2), do.stride(1))
+        else:
+            o_str, g_str = o.stride()[:3], do.stride()[:3]
+        dq = torch.empty(B, h, Sq, d, dtype=q.dtype, device=q.device)
+        dk = torch.empty(B, h, Sk, d, dtype=q.dtype, device=q.device)
+        dv = torch.empty(B, h, Sk, d, dtype=q.dtype, device=q.device)
+        delta = torch.empty(B * h, Sq, dtype=torch.float32, device=q.device)
+        N.count_launch(4 if d > 128 else 3)
+        N.call("smpk_attn_bwd", N.stream_ptr(q.device), N.dtype_code(q.dtype), B, h, Sq, Sk, d,
+               q.data_ptr(), *q.stride()[:3], k.data_ptr(), *k.stride()[:3], v.data_ptr(), *v.stride()[:3],
+               o.data_ptr(), *o_str, do.data_ptr(), *g_str, lse.data_ptr(), delta.data_ptr(),
+               dq.data_ptr(), *dq.stride()[:3], dk.data_ptr(), *dk.stride()[:3], dv.data_ptr(), *dv.stride()[:3],
+               scale, causal, window, *_mask_args(mask), p_drop, seed, offset)
+        return dq, dk, dv, None, None, None, None, None, None, None, None
 
-        q, k, v, probs = ctx.saved_tensors
-        dout = dout.contiguous()
-        BH, S, d = q.shape
-        dv = gemm(probs, dout, a_mn_major=True, b_mn_major=True, causal="lower_at")      # P^T dO
-        dp = torch.empty_like(probs)
-        gemm(dout, v, out=dp, causal="lower_out")                                        # dO V^T (lower tiles)
-        ds = torch.empty_like(probs)
-        N.count_launch()
-        N.call("smpk_softmax_bwd", N.stream_ptr(q.device), dp.data_ptr(), probs.data_ptr(), ds.data_ptr(),
-               N.dtype_code(q.dtype), 2, float(ctx.scale), BH, S, S)
-        del dp
-        a = ctx.gemm_scale
-        dq = gemm(ds, k, b_mn_major=True, causal="lower_a", alpha=a)                     # dS K
-        dk = gemm(ds, q, a_mn_major=True, b_mn_major=True, causal="lower_at", alpha=a)   # dS^T Q
-        return dq, dk, dv, None, None
+
+def flash_applicable(q, k, v) -> bool:
+    d = q.shape[-1]
+    return (q.is_cuda and q.dtype in (torch.bfloat16, torch.float16) and k.dtype == q.dtype and v.dtype == q.dtype
+            and d % 32 == 0 and 32 <= d <= 256 and v.shape[-1] == d)
 
 
-def _causal_fast_path(q, k, mask, window, dropout_p, training) -> bool:
-    return (q.is_cuda and mask is None and window is None and q.shape[2] == k.shape[2] and q.shape[2] % 8 == 0 and q.shape[2] <= 8192
-            and q.shape[3] % 8 == 0 and q.dtype in (torch.bfloat16, torch.float16) and not (dropout_p > 0.0 and training)
-            and N.available())
+def _dropout_counter():
+    """(seed, offset) for the counter-based dropout of one attention call, drawn from the CPU generator: no device
+    synchronisation, and an activation-checkpoint recomputation (which restores the generator) redraws the same."""
+    r = torch.randint(0, 2 ** 31 - 1, (2,), dtype=torch.int64)
+    return int(torch.initial_seed()) & (2 ** 63 - 1), (int(r[0]) << 31) | int(r[1])
 
 
 # --------------------------------------------------------------------------------- core attention
 def core_attention(q, k, v, *, causal: bool = True, mask=None, scale: float | None = None, dropout_p: float = 0.0,
-                   training: bool = True, window: int | None = None, gemm_scale: float = 1.0):
-    """softmax(scale * q k^T + mask) v for q,k,v [B, heads, S, d]; returns [B, heads, Sq, d].
+                   training: bool = True, window: int | None = None, gemm_scale: float = 1.0,
+                   token_major: bool = False):
+    """softmax(scale * q k^T + mask) v for q,k,v [B, heads, S, d]; returns [B, heads, Sq, d], or [B, Sq, heads, d]
+    with ``token_major``.
 
-    ``mask`` is a uint8/bool [B,1,Sq,Sk] tensor whose non-zero entries are excluded; ``causal`` applies
-    the lower-triangular mask; ``window`` (local attention) is folded into the byte mask.  ``gemm_scale`` is the
-    part of ``scale`` applied by the score GEMM itself (the stored 16-bit scores are ``gemm_scale * q k^T``, the
-    softmax applies the rest) - the reference's ``query_key_layer_scaling`` / ``attention_in_fp32`` guard against
-    fp16 overflow of the raw scores (reference torch/nn/transformer.py:1769-1835).
+    ``mask`` is a uint8/bool [B,1,Sq|1,Sk] tensor whose non-zero entries are excluded; ``causal`` applies the
+    lower-triangular mask (aligned to the last key when Sq != Sk); ``window`` restricts every query to the last
+    ``window`` visible keys (local attention).  ``gemm_scale`` is accepted for the reference's
+    ``query_key_layer_scaling`` / ``attention_in_fp32`` options (reference torch/nn/transformer.py:1769-1835): their
+    purpose - keeping 16-bit scores in range - is moot here because scores only exist as fp32 accumulators in
+    tensor memory, so it does not change the result.
     """
     B, h, Sq, d = q.shape
     Sk = k.shape[2]
     scale = (1.0 / math.sqrt(d)) if scale is None else scale
-    if causal and _causal_fast_path(q, k, mask, window, dropout_p, training):
-        ctx = _CausalAttention.apply(q.reshape(B * h, Sq, d).contiguous(), k.reshape(B * h, Sk, d).contiguous(),
-                                     v.reshape(B * h, Sk, d).contiguous(), float(scale / gemm_scale), float(gemm_scale))
-        return ctx.reshape(B, h, Sq, d)
-    scores = bmm_nt(q.reshape(B * h, Sq, d), k.reshape(B * h, Sk, d), alpha=gemm_scale)
-    scale = scale / gemm_scale
-    if window is not None:
+    p_drop = float(dropout_p) if training else 0.0
+    if mask is not None:
+        mask = mask.to(torch.uint8) if mask.dtype != torch.uint8 else mask
+        if mask.dim() != 4 or mask.stride(-1) != 1:
+            mask = mask.reshape(mask.shape[0], 1, -1, mask.shape[-1]).contiguous()
+    if flash_applicable(q, k, v):
+        seed, offset = _dropout_counter() if p_drop > 0.0 else (0, 0)
+        return _FlashAttention.apply(q, k, v, mask, float(scale), bool(causal), int(window or 0), p_drop, seed, offset,
+                                     token_major)
+    # CPU tensors, fp32 or head sizes the kernels do not tile: the library's scaled-dot-product attention
+    dead = None
+    if causal or window:
         i = torch.arange(Sq, device=q.device)[:, None] + (Sk - Sq)
         j = torch.arange(Sk, device=q.device)[None, :]
-        wmask = ((j > i) if causal else torch.zeros(Sq, Sk, dtype=torch.bool, device=q.device)) | (j <= i - window)
-        wmask = wmask[None, None].expand(B, 1, Sq, Sk)
-        mask = wmask if mask is None else (mask.bool() | wmask)
-        causal = False
+        dead = (j > i) if causal else torch.zeros(Sq, Sk, dtype=torch.bool, device=q.device)
+        if window:
+            dead = dead | (j <= i - window)
+        dead = dead[None, None]
     if mask is not None:
-        if causal:
-            tri = torch.ones(Sq, Sk, dtype=torch.bool, device=q.device).triu(diagonal=1 + Sk - Sq)
-            mask = mask.bool() | tri[None, None]
-        probs = scaled_masked_softmax(scores.reshape(B, h, Sq, Sk), mask, scale).reshape(B * h, Sq, Sk)
-    elif causal:
-        probs = scaled_upper_triang_masked_softmax(scores, scale)
-    else:
-        probs = scaled_masked_softmax(scores.reshape(B, h, Sq, Sk), None, scale).reshape(B * h, Sq, Sk)
-    if dropout_p > 0.0 and training:
-        probs = torch.nn.functional.dropout(probs, dropout_p, True)
-    ctx = bmm_nn(probs, v.reshape(B * h, Sk, d))
-    return ctx.reshape(B, h, Sq, d)
+        dead = mask.bool() if dead is None else (dead | mask.bool())
+    keep = None if dead is None else ~dead
+    out = torch.nn.functional.scaled_dot_product_attention(q, k, v, attn_mask=keep, dropout_p=p_drop, scale=scale)
+    if keep is not None:
+        out = torch.nan_to_num(out, nan=0.0)            # rows without a visible key
+    return out.transpose(1, 2).contiguous() if token_major else out

@@ -423,16 +423,30 @@ class ShardedDataParallelEngine:
         if u.users <= 0:
             self._release(u)
 
+    def _adam_in_backward(self) -> bool:
+        """Opt-in (config ``sdp_adam_in_backward: true`` or ``SMP_SDP_FUSED_ADAM=1``): the reduce kernel of the last
+        microbatch also applies Adam and rewrites the 16-bit shard, i.e. the parameter update happens inside
+        ``model.backward`` and ``optimizer.step()`` only does the bookkeeping.  Consequences the caller accepts with
+        the opt-in: skipping ``optimizer.step()`` does not skip the update, ``grad_norm()`` sees no gradient for the
+        units already updated, and the first ``clip_master_grads`` call switches the engine back to the ordinary
+        order (reduce in backward, clip + Adam in ``optimizer.step()``) from the next step on.  Off by default."""
+        env = os.environ.get("SMP_SDP_FUSED_ADAM")
+        if env is not None:
+            return env == "1"
+        return bool(getattr(self.state.cfg, "sdp_adam_in_backward", False))
+
     def _fused_adam_args(self, u: Unit):
         """Hyper-parameters for applying Adam inside the reduce kernel, or None when the update has to wait:
-        not the last microbatch, a global quantity is needed first (clipping, dynamic loss scale), gradients
-        still have to cross replica groups, or the optimizer is not Adam/AdamW."""
+        the opt-in is off, not the last microbatch, a global quantity is needed first (clipping, dynamic loss
+        scale), gradients still have to cross replica groups, or the optimizer is not Adam/AdamW."""
         opt = self.optimizer
+        if not self._adam_in_backward():
+            return None
         if opt is None or (self.clip and self.clip > 0) or self.dynamic or self.loss_scale != 1.0:
             return None
         if self.replica_group is not None and dist.get_world_size(self.replica_group) > 1:
             return None
-        if type(opt).__name__ not in ("Adam", "AdamW", "FusedAdam") or os.environ.get("SMP_SDP_FUSED_ADAM", "1") == "0":
+        if type(opt).__name__ not in ("Adam", "AdamW", "FusedAdam"):
             return None
         if self.state.microbatch != self.state.num_microbatches() - 1 or not self._sync_step:
             return None
@@ -462,6 +476,14 @@ class ShardedDataParallelEngine:
     # ------------------------------------------------------------------ DistributedModel entry points
     def forward(self, module, args, kwargs):
         self._build()
+        if self.state.microbatch == 0 and any(u.updated for u in self.units):
+            # in-backward Adam ran last step but optimizer.step() was never called: the update is already in the
+            # shards, so close that step here (bias-correction count, flags, peers' view of the parameters)
+            self._step += 1
+            for u in self.units:
+                u.updated = False
+            if self.fabric is not None:
+                self.fabric.publish_params()
         for u in self.units:
             u.calls_in_mb = 0
         out = module(*args, **kwargs)

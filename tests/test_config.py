@@ -127,3 +127,9 @@ def test_fused_tp_collectives_key_selects_the_comm_mode(monkeypatch):
     assert tp_ops.get_comm_mode() == "nccl"
     smp.init({"microbatches": 1})
     assert tp_ops.get_comm_mode() == ("fused" if torch.cuda.is_available() else "nccl")
+
+
+def test_sdp_adam_in_backward_is_opt_in():
+    """Applying the sharded Adam update inside backward changes when parameters move, so it is off unless asked for."""
+    assert ModelParallelConfig({}).sdp_adam_in_backward is False
+    assert ModelParallelConfig({"sdp_adam_in_backward": True}).sdp_adam_in_backward is True

@@ -25,6 +25,8 @@ def _worker(rank, world, fused, clip, ckpt_offload=False):
 
     os.environ["SMP_SDP_UNIT_ELEMENTS"] = "250000"
     os.environ["SMP_SDP_FUSED"] = "1" if fused else "0"
+    # without clipping, also exercise the opt-in that applies Adam inside the reduce kernel during backward
+    os.environ["SMP_SDP_FUSED_ADAM"] = "1" if (fused and clip == 0) else "0"
     smp.init({"sharded_data_parallel_degree": world, "microbatches": 2, "bf16": True, "ddp": True,
               "sdp_param_persistence_threshold": 1000, "sdp_gradient_clipping": clip,
               "offload_activations": ckpt_offload})
