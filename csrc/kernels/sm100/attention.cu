@@ -227,19 +227,17 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     if (lane == 0 && ntiles > 0) {
       const uint64_t hi_k = make_smem_desc_hi(16, 1024);              // K-major operands (Q, K)
       const uint64_t hi_v = make_smem_desc_hi(BN * 128, 1024);        // V as the N-major B operand of P V
-      const int ksteps_s = p.d / 16;                                  // reduction over head_dim
       int kst = 0, vst = 0;
       uint32_t kph = 0, vph = 0;
       auto issue_s = [&](int t) {   // S_t = Q K_t^T into score buffer t & 1
         mbar_wait(&k_full[kst], kph);
         tc_fence_after();
         const uint32_t tmem_s = tmem_base + (t & 1) * BN;
-        for (int ks = 0; ks < ksteps_s; ++ks) {
-          const int c = ks >> 2, within = (ks & 3) * 32;
-          const uint64_t da = make_smem_desc(sQ + c * (BM * 128) + within, hi_k);
-          const uint64_t db = make_smem_desc(sK + kst * C::KV_BYTES + c * (BN * 128) + within, hi_k);
-          umma_f16(tmem_s, da, db, p.idesc_s, ks != 0);
-        }
+        // reduction over the padded head_dim (TMA zero-fills the columns beyond d): a compile-time MMA count
+#pragma unroll
+        for (int ks = 0; ks < NCH * 4; ++ks)
+          umma_f16(tmem_s, make_smem_desc(sQ + (ks >> 2) * (BM * 128) + (ks & 3) * 32, hi_k),
+                   make_smem_desc(sK + kst * C::KV_BYTES + (ks >> 2) * (BN * 128) + (ks & 3) * 32, hi_k), p.idesc_s, ks != 0);
         umma_commit(&k_empty[kst]);
         umma_commit(&s_full[t & 1]);
         if (++kst == KST) { kst = 0; kph ^= 1; }
@@ -253,10 +251,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         tc_fence_after();
         const uint32_t tmem_p = tmem_base + (t & 1) * BN;             // P_t packed over the first BN/2 columns of S_t
 #pragma unroll
-        for (int ks = 0; ks < BN / 16; ++ks) {
-          const uint64_t db = make_smem_desc(sV + vst * C::KV_BYTES + ks * (16 * 128), hi_v);
-          umma_f16_ts(tmem_o, tmem_p + ks * 8, db, p.idesc_o, (t != 0) || ks != 0);
-        }
+        for (int ks = 0; ks < BN / 16; ++ks)
+          umma_f16_ts(tmem_o, tmem_p + ks * 8, make_smem_desc(sV + vst * C::KV_BYTES + ks * (16 * 128), hi_v), p.idesc_o,
+                      (t != 0) || ks != 0);
         umma_commit(&v_empty[vst]);
         umma_commit(o_bar);
         if (++vst == VST) { vst = 0; vph ^= 1; }
@@ -500,12 +497,12 @@ struct BwdParams {
   uint32_t idesc_t, idesc_o;
 };
 
-template <int NCH, int BS, int YST, bool NEED_X2>
+template <int NCH, int BS, int Y1ST, int Y2ST, bool NEED_X2>
 struct BwdCfg {
   static constexpr int X_BYTES = NCH * BM * 128;             // one resident operand
   static constexpr int Y_BYTES = NCH * BS * 128;             // one streamed operand tile
   static constexpr int STAT_BYTES = 2 * 2 * BS * 4;          // lse / delta of the streamed queries, double buffered
-  static constexpr int SMEM_BYTES = (NEED_X2 ? 2 : 1) * X_BYTES + 2 * YST * Y_BYTES + STAT_BYTES + 1024 + 256;
+  static constexpr int SMEM_BYTES = (NEED_X2 ? 2 : 1) * X_BYTES + (Y1ST + Y2ST) * Y_BYTES + STAT_BYTES + 1024 + 256;
 };
 
 constexpr int BWD_THREADS = 384;   // warps 0-3: producers / MMA / TMEM, warps 4-11: two elementwise warpgroups
@@ -534,7 +531,10 @@ __device__ __forceinline__ uint32_t pack2(float a, float b, int dtype) {
 // OUT_P : accumulate P^T dO_i  (dV)           - only with TR
 // OUT_DS: accumulate dS^T Q_i (dK) with TR, dS K_j (dQ) without
 // GENERAL = false: no byte mask and no dropout - the straight-line elementwise stage.
-template <int NCH, int BS, int YST, bool TR, bool OUT_P, bool OUT_DS, bool GENERAL>
+// Y1ST / Y2ST: ring depth of the two streamed operands.  The first one is read by a score product and by an output
+// product of the same tile, so it needs two stages for the score products to run one tile ahead; the second one
+// is read only by the second score product when dV is not accumulated here and then gets by with one stage.
+template <int NCH, int BS, int Y1ST, int Y2ST, bool TR, bool OUT_P, bool OUT_DS, bool GENERAL>
 __global__ void __launch_bounds__(BWD_THREADS, 1)
     attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_x1, const __grid_constant__ CUtensorMap tma_x2,
                     const __grid_constant__ CUtensorMap tma_y1, const __grid_constant__ CUtensorMap tma_y2,
@@ -542,7 +542,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   constexpr bool NEED_T2 = OUT_DS;              // dP is only needed for dS
   constexpr bool NEED_X2 = NEED_T2;
   constexpr bool NEED_Y2 = NEED_T2 || OUT_P;
-  using C = BwdCfg<NCH, BS, YST, NEED_X2>;
+  using C = BwdCfg<NCH, BS, Y1ST, Y2ST, NEED_X2>;
+  static_assert(Y1ST >= 2 && (Y2ST >= 2 || (!OUT_P && Y2ST == 1)), "ring depths");
   constexpr int HC = BS / 2;                    // columns of a score tile handled by one elementwise warpgroup
   constexpr int DPAD = NCH * 64;
   extern __shared__ uint8_t smem_raw[];
@@ -550,15 +551,15 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   uint8_t* sX1 = smem;
   uint8_t* sX2 = sX1 + C::X_BYTES;
   uint8_t* sY1 = sX1 + (NEED_X2 ? 2 : 1) * C::X_BYTES;
-  uint8_t* sY2 = sY1 + YST * C::Y_BYTES;
-  float* sStat = reinterpret_cast<float*>(sY2 + YST * C::Y_BYTES);     // [2][2][BS]
+  uint8_t* sY2 = sY1 + Y1ST * C::Y_BYTES;
+  float* sStat = reinterpret_cast<float*>(sY2 + Y2ST * C::Y_BYTES);     // [2][2][BS]
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sStat) + C::STAT_BYTES);
   uint64_t* x_full = bars;
   uint64_t* y1_full = bars + 1;
-  uint64_t* y1_empty = y1_full + YST;
-  uint64_t* y2_full = y1_empty + YST;
-  uint64_t* y2_empty = y2_full + YST;
-  uint64_t* t_full = y2_empty + YST;       // [2] MMA -> elementwise: score tiles of buffer b complete
+  uint64_t* y1_empty = y1_full + Y1ST;
+  uint64_t* y2_full = y1_empty + Y1ST;
+  uint64_t* y2_empty = y2_full + Y2ST;
+  uint64_t* t_full = y2_empty + Y2ST;      // [2] MMA -> elementwise: score tiles of buffer b complete
   uint64_t* pd_full = t_full + 2;          // [2] elementwise -> MMA: P / dS of buffer b written (8 warp arrivals)
   uint64_t* acc_done = pd_full + 2;        // [1]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_done + 1);
@@ -590,10 +591,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   }
   if (warp == 1 && lane == 0) {
     mbar_init(x_full, 1);
-    for (int i = 0; i < YST; ++i) {
-      mbar_init(&y1_full[i], 1); mbar_init(&y1_empty[i], 1);
-      mbar_init(&y2_full[i], 1); mbar_init(&y2_empty[i], 1);
-    }
+    for (int i = 0; i < Y1ST; ++i) { mbar_init(&y1_full[i], 1); mbar_init(&y1_empty[i], 1); }
+    for (int i = 0; i < Y2ST; ++i) { mbar_init(&y2_full[i], 1); mbar_init(&y2_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], 1); mbar_init(&pd_full[i], 8); }
     mbar_init(acc_done, 1);
     fence_mbar_init();
@@ -626,7 +625,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
 #pragma unroll
         for (int c = 0; c < NCH; ++c)
           tma_load_4d(sY1 + st * C::Y_BYTES + c * (BS * 128), &tma_y1, &y1_full[st], c * 64, i * BS, h, b);
-        if (++st == YST) { st = 0; ph ^= 1; }
+        if (++st == Y1ST) { st = 0; ph ^= 1; }
       }
     }
   } else if (warp == 3) {
@@ -640,7 +639,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
 #pragma unroll
         for (int c = 0; c < NCH; ++c)
           tma_load_4d(sY2 + st * C::Y_BYTES + c * (BS * 128), &tma_y2, &y2_full[st], c * 64, i * BS, h, b);
-        if (++st == YST) { st = 0; ph ^= 1; }
+        if (++st == Y2ST) { st = 0; ph ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -648,30 +647,30 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
     if (lane == 0 && ntiles > 0) {
       const uint64_t hi_k = make_smem_desc_hi(16, 1024);            // K-major operands of the score products
       const uint64_t hi_n = make_smem_desc_hi(BS * 128, 1024);      // streamed tile as the N-major B of an output product
-      const int ksteps = p.d / 16;
-      int st_t = 0, st_o = 0;
-      uint32_t ph_t = 0;
+      int t1 = 0, t2 = 0, o1 = 0, o2 = 0;          // ring positions: score products (t*) and output products (o*)
+      uint32_t ph1 = 0, ph2 = 0, oph2 = 0;
       auto issue_t = [&](int t) {
         const uint32_t tm = tmem_base + (t & 1) * (2 * BS);
-        mbar_wait(&y1_full[st_t], ph_t);
+        mbar_wait(&y1_full[t1], ph1);
         tc_fence_after();
-        for (int ks = 0; ks < ksteps; ++ks) {
-          const int c = ks >> 2, within = (ks & 3) * 32;
-          umma_f16(tm, make_smem_desc(sX1 + c * (BM * 128) + within, hi_k),
-                   make_smem_desc(sY1 + st_t * C::Y_BYTES + c * (BS * 128) + within, hi_k), p.idesc_t, ks != 0);
-        }
+        // the reduction runs over the padded head_dim (NCH * 64 columns; TMA zero-fills the padding), so the number
+        // of MMAs is a compile-time constant and the loop unrolls without predication
+#pragma unroll
+        for (int ks = 0; ks < NCH * 4; ++ks)
+          umma_f16(tm, make_smem_desc(sX1 + (ks >> 2) * (BM * 128) + (ks & 3) * 32, hi_k),
+                   make_smem_desc(sY1 + t1 * C::Y_BYTES + (ks >> 2) * (BS * 128) + (ks & 3) * 32, hi_k), p.idesc_t, ks != 0);
         if (NEED_T2) {
-          mbar_wait(&y2_full[st_t], ph_t);
+          mbar_wait(&y2_full[t2], ph2);
           tc_fence_after();
-          for (int ks = 0; ks < ksteps; ++ks) {
-            const int c = ks >> 2, within = (ks & 3) * 32;
-            umma_f16(tm + BS, make_smem_desc(sX2 + c * (BM * 128) + within, hi_k),
-                     make_smem_desc(sY2 + st_t * C::Y_BYTES + c * (BS * 128) + within, hi_k), p.idesc_t, ks != 0);
-          }
-          if (!OUT_P) umma_commit(&y2_empty[st_t]);     // the second streamed operand is not read again
+#pragma unroll
+          for (int ks = 0; ks < NCH * 4; ++ks)
+            umma_f16(tm + BS, make_smem_desc(sX2 + (ks >> 2) * (BM * 128) + (ks & 3) * 32, hi_k),
+                     make_smem_desc(sY2 + t2 * C::Y_BYTES + (ks >> 2) * (BS * 128) + (ks & 3) * 32, hi_k), p.idesc_t, ks != 0);
+          if (!OUT_P) umma_commit(&y2_empty[t2]);     // the second streamed operand is not read again
+          if (++t2 == Y2ST) { t2 = 0; ph2 ^= 1; }
         }
         umma_commit(&t_full[t & 1]);
-        if (++st_t == YST) { st_t = 0; ph_t ^= 1; }
+        if (++t1 == Y1ST) { t1 = 0; ph1 ^= 1; }
       };
       mbar_wait(x_full, 0);
       issue_t(0);
@@ -683,24 +682,25 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
         if (OUT_P) {
           // (the streamed dO tile was already waited for by issue_t when NEED_T2; otherwise wait here)
           if (!NEED_T2) {
-            mbar_wait(&y2_full[st_o], ((t / YST) & 1));
+            mbar_wait(&y2_full[o2], oph2);
             tc_fence_after();
           }
 #pragma unroll
           for (int ks = 0; ks < BS / 16; ++ks)
-            umma_f16_ts(tmem_acc0, tm + ks * 8, make_smem_desc(sY2 + st_o * C::Y_BYTES + ks * (16 * 128), hi_n),
-                        p.idesc_o, (t != 0) || ks != 0);
-          umma_commit(&y2_empty[st_o]);
+            umma_f16_ts(tmem_acc0, tm + (ks / (HC / 16)) * HC + (ks % (HC / 16)) * 8,
+                        make_smem_desc(sY2 + o2 * C::Y_BYTES + ks * (16 * 128), hi_n), p.idesc_o, (t != 0) || ks != 0);
+          umma_commit(&y2_empty[o2]);
+          if (++o2 == Y2ST) { o2 = 0; oph2 ^= 1; }
         }
         if (OUT_DS) {
           const uint32_t acc = OUT_P ? tmem_acc1 : tmem_acc0;
 #pragma unroll
           for (int ks = 0; ks < BS / 16; ++ks)
-            umma_f16_ts(acc, tm + BS + ks * 8, make_smem_desc(sY1 + st_o * C::Y_BYTES + ks * (16 * 128), hi_n),
-                        p.idesc_o, (t != 0) || ks != 0);
+            umma_f16_ts(acc, tm + BS + (ks / (HC / 16)) * HC + (ks % (HC / 16)) * 8,
+                        make_smem_desc(sY1 + o1 * C::Y_BYTES + ks * (16 * 128), hi_n), p.idesc_o, (t != 0) || ks != 0);
         }
-        umma_commit(&y1_empty[st_o]);
-        if (++st_o == YST) st_o = 0;
+        umma_commit(&y1_empty[o1]);
+        if (++o1 == Y1ST) o1 = 0;
       }
       umma_commit(acc_done);
     }
@@ -801,8 +801,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
         dpk[i >> 1] = pack2(dv[0], dv[1], p.dtype);
         dpk[(i >> 1) + 1] = pack2(dv[2], dv[3], p.dtype);
       }
-      if (OUT_P) tmem_st_n<HC / 2>(tm + g * (HC / 2), ppk);
-      if (OUT_DS) tmem_st_n<HC / 2>(tm + BS + g * (HC / 2), dpk);
+      // (each warpgroup overwrites only columns it has just read itself: P / dS of half g live at the start of that half)
+      if (OUT_P) tmem_st_n<HC / 2>(tm + g * HC, ppk);
+      if (OUT_DS) tmem_st_n<HC / 2>(tm + BS + g * HC, dpk);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -854,14 +855,14 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
   }
 }
 
-template <int NCH, int BS, int YST, bool TR, bool OUT_P, bool OUT_DS, bool GENERAL>
+template <int NCH, int BS, int Y1ST, int Y2ST, bool TR, bool OUT_P, bool OUT_DS, bool GENERAL>
 int launch_bwd_g(const CUtensorMap& x1, const CUtensorMap& x2, const CUtensorMap& y1, const CUtensorMap& y2,
                  const BwdParams& p, cudaStream_t stream) {
-  using C = BwdCfg<NCH, BS, YST, OUT_DS>;
+  using C = BwdCfg<NCH, BS, Y1ST, Y2ST, OUT_DS>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
-  auto kern = attn_bwd_kernel<NCH, BS, YST, TR, OUT_P, OUT_DS, GENERAL>;
+  auto kern = attn_bwd_kernel<NCH, BS, Y1ST, Y2ST, TR, OUT_P, OUT_DS, GENERAL>;
   if (!attr_set[dev & 63]) {
     SMPK_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_set[dev & 63] = true;
@@ -872,12 +873,12 @@ int launch_bwd_g(const CUtensorMap& x1, const CUtensorMap& x2, const CUtensorMap
   SMPK_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
-template <int NCH, int BS, int YST, bool TR, bool OUT_P, bool OUT_DS>
+template <int NCH, int BS, int Y1ST, int Y2ST, bool TR, bool OUT_P, bool OUT_DS>
 int launch_bwd(const CUtensorMap& x1, const CUtensorMap& x2, const CUtensorMap& y1, const CUtensorMap& y2,
                const BwdParams& p, cudaStream_t stream) {
   if (p.m.mask != nullptr || p.drop.enabled)
-    return launch_bwd_g<NCH, BS, YST, TR, OUT_P, OUT_DS, true>(x1, x2, y1, y2, p, stream);
-  return launch_bwd_g<NCH, BS, YST, TR, OUT_P, OUT_DS, false>(x1, x2, y1, y2, p, stream);
+    return launch_bwd_g<NCH, BS, Y1ST, Y2ST, TR, OUT_P, OUT_DS, true>(x1, x2, y1, y2, p, stream);
+  return launch_bwd_g<NCH, BS, Y1ST, Y2ST, TR, OUT_P, OUT_DS, false>(x1, x2, y1, y2, p, stream);
 }
 
 }  // namespace
@@ -966,51 +967,45 @@ SMPK_API int smpk_attn_bwd(void* stream, int dtype, int B, int H, int Sq, int Sk
   p.lse = lse; p.delta = delta; p.dtype = dtype;
   const uint32_t fmt = dtype == SMPK_BF16 ? 1u : 0u;
   const int nch = (d + 63) / 64;
-  const int BS = nch == 4 ? 32 : 64;           // head_dim 256: 32-row streamed tiles so that two stages fit
+  const int BS = 64;                           // rows of a streamed tile
   CUtensorMap tq_res, tdo_res, tk_res, tv_res, tq_str, tdo_str, tk_str, tv_str;
   int rc;
   if ((rc = make_map4(&tq_res, dtype, q, B, H, Sq, d, q_sb, q_sh, q_ss, BM))) return rc;
   if ((rc = make_map4(&tdo_res, dtype, d_o, B, H, Sq, d, g_sb, g_sh, g_ss, BM))) return rc;
   if ((rc = make_map4(&tk_res, dtype, k, B, H, Sk, d, k_sb, k_sh, k_ss, BM))) return rc;
   if ((rc = make_map4(&tv_res, dtype, v, B, H, Sk, d, v_sb, v_sh, v_ss, BM))) return rc;
-  // streamed tiles; the key-stationary pass that only accumulates dV at head_dim 256 streams 64 rows
-  const int BS_A1 = 64;
   if ((rc = make_map4(&tk_str, dtype, k, B, H, Sk, d, k_sb, k_sh, k_ss, BS))) return rc;
   if ((rc = make_map4(&tv_str, dtype, v, B, H, Sk, d, v_sb, v_sh, v_ss, BS))) return rc;
+  if ((rc = make_map4(&tq_str, dtype, q, B, H, Sq, d, q_sb, q_sh, q_ss, BS))) return rc;
+  if ((rc = make_map4(&tdo_str, dtype, d_o, B, H, Sq, d, g_sb, g_sh, g_ss, BS))) return rc;
+  p.idesc_t = make_idesc_f16(fmt, 0, 0, BM, BS);
+  p.idesc_o = make_idesc_f16(fmt, 0, 1, BM, d);
   // ---- query-stationary pass: dQ
   p.out_p = nullptr;
   p.out_ds = dq; p.s_sb = dq_sb; p.s_sh = dq_sh; p.s_ss = dq_ss;
-  p.idesc_t = make_idesc_f16(fmt, 0, 0, BM, BS);
-  p.idesc_o = make_idesc_f16(fmt, 0, 1, BM, d);
   switch (nch) {
-    case 1: rc = launch_bwd<1, 64, 3, false, false, true>(tq_res, tdo_res, tk_str, tv_str, p, s); break;
-    case 2: rc = launch_bwd<2, 64, 2, false, false, true>(tq_res, tdo_res, tk_str, tv_str, p, s); break;
-    case 3: rc = launch_bwd<3, 64, 2, false, false, true>(tq_res, tdo_res, tk_str, tv_str, p, s); break;
-    default: rc = launch_bwd<4, 32, 2, false, false, true>(tq_res, tdo_res, tk_str, tv_str, p, s); break;
+    case 1: rc = launch_bwd<1, 64, 3, 3, false, false, true>(tq_res, tdo_res, tk_str, tv_str, p, s); break;
+    case 2: rc = launch_bwd<2, 64, 2, 2, false, false, true>(tq_res, tdo_res, tk_str, tv_str, p, s); break;
+    case 3: rc = launch_bwd<3, 64, 2, 2, false, false, true>(tq_res, tdo_res, tk_str, tv_str, p, s); break;
+    default: rc = launch_bwd<4, 64, 2, 1, false, false, true>(tq_res, tdo_res, tk_str, tv_str, p, s); break;
   }
   if (rc) return rc;
   // ---- key-stationary pass(es): dK, dV
-  if ((rc = make_map4(&tq_str, dtype, q, B, H, Sq, d, q_sb, q_sh, q_ss, BS))) return rc;
-  if ((rc = make_map4(&tdo_str, dtype, d_o, B, H, Sq, d, g_sb, g_sh, g_ss, BS))) return rc;
   p.out_p = dv; p.p_sb = dv_sb; p.p_sh = dv_sh; p.p_ss = dv_ss;
   p.out_ds = dk; p.s_sb = dk_sb; p.s_sh = dk_sh; p.s_ss = dk_ss;
   switch (nch) {
-    case 1: return launch_bwd<1, 64, 3, true, true, true>(tk_res, tv_res, tq_str, tdo_str, p, s);
-    case 2: return launch_bwd<2, 64, 2, true, true, true>(tk_res, tv_res, tq_str, tdo_str, p, s);
+    case 1: return launch_bwd<1, 64, 3, 3, true, true, true>(tk_res, tv_res, tq_str, tdo_str, p, s);
+    case 2: return launch_bwd<2, 64, 2, 2, true, true, true>(tk_res, tv_res, tq_str, tdo_str, p, s);
     case 3: {
       // 192 padded columns: two accumulators (384) + score tiles (256) exceed tensor memory - split like head_dim 256
-      rc = launch_bwd<3, 64, 2, true, false, true>(tk_res, tv_res, tq_str, tdo_str, p, s);
+      rc = launch_bwd<3, 64, 2, 2, true, false, true>(tk_res, tv_res, tq_str, tdo_str, p, s);
       if (rc) return rc;
-      return launch_bwd<3, 64, 2, true, true, false>(tk_res, tv_res, tq_str, tdo_str, p, s);
+      return launch_bwd<3, 64, 2, 2, true, true, false>(tk_res, tv_res, tq_str, tdo_str, p, s);
     }
     default: {
-      rc = launch_bwd<4, 32, 2, true, false, true>(tk_res, tv_res, tq_str, tdo_str, p, s);      // dK
+      rc = launch_bwd<4, 64, 2, 1, true, false, true>(tk_res, tv_res, tq_str, tdo_str, p, s);      // dK
       if (rc) return rc;
-      CUtensorMap tq64, tdo64;
-      if ((rc = make_map4(&tq64, dtype, q, B, H, Sq, d, q_sb, q_sh, q_ss, BS_A1))) return rc;
-      if ((rc = make_map4(&tdo64, dtype, d_o, B, H, Sq, d, g_sb, g_sh, g_ss, BS_A1))) return rc;
-      p.idesc_t = make_idesc_f16(fmt, 0, 0, BM, BS_A1);
-      return launch_bwd<4, 64, 2, true, true, false>(tk_res, tv_res, tq64, tdo64, p, s);          // dV
+      return launch_bwd<4, 64, 2, 2, true, true, false>(tk_res, tv_res, tq_str, tdo_str, p, s);    // dV
     }
   }
 }
