@@ -15,6 +15,9 @@ optimizer step per timed step.  Rank 0 prints ONE JSON line.
 
 `--impl reference` would run the unmodified reference; it cannot be installed here (binary-only wheel
 with its native libraries missing), so that arm reports `unavailable`.
+`--impl baseline` runs the reference's hot path restated with stock PyTorch + NCCL (package `baseline/`, nothing
+of this library on that path) for the same model / N / batch geometry; its measured tokens/s are kept in
+`baseline/measured.json` and the product line reports `vs_baseline` against them.
 """
 
 from __future__ import annotations
@@ -116,109 +119,6 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def library_baseline(args):
-    """N=1 stand-in for the reference's compute path: the stock HuggingFace GPT-J module (cuBLAS GEMMs through
-    F.linear, library attention / LayerNorm / softmax kernels), fp32 master weights with bf16 autocast and
-    torch's fused AdamW - none of this repo's kernels or engine.  Same model, batch geometry and timing."""
-    import torch
-    from transformers import GPTJConfig, GPTJForCausalLM
-
-    from smdistributed_modelparallel_b200.models.configs import MODEL_CONFIGS, param_count, train_flops_per_token
-
-    mcfg = dict(MODEL_CONFIGS[args.model])
-    if args.layers:
-        mcfg["num_layers"] = args.layers
-    seq = args.seq or mcfg["num_positions"]
-    dev = torch.device("cuda", 0)
-    torch.manual_seed(1234)
-    vocab = mcfg["vocab_size"]
-    total_seqs = (args.micro_batch or 4) * (args.microbatches or 2)
-
-    def build(attn, micro):
-        cfg = GPTJConfig(vocab_size=mcfg["vocab_size"], n_positions=seq, n_embd=mcfg["hidden_size"],
-                         n_layer=mcfg["num_layers"], n_head=mcfg["num_attention_heads"], rotary_dim=mcfg["rotary_dim"],
-                         n_inner=mcfg["intermediate_size"], resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0,
-                         use_cache=False)
-        cfg._attn_implementation = attn
-        with torch.device(dev):
-            model = GPTJForCausalLM(cfg)
-        model.train()
-        opt = torch.optim.AdamW(model.parameters(), lr=1e-4, betas=(0.9, 0.95), weight_decay=0.1, fused=True)
-        nmb = total_seqs // micro
-
-        def one_step(ids):
-            opt.zero_grad(set_to_none=True)
-            total = None
-            for mb in range(nmb):
-                chunk = ids[mb * micro:(mb + 1) * micro]
-                with torch.autocast("cuda", dtype=torch.bfloat16):
-                    loss = model(input_ids=chunk, labels=chunk).loss / nmb
-                loss.backward()
-                total = loss.detach() if total is None else total + loss.detach()
-            opt.step()
-            return total
-
-        return model, opt, one_step, nmb
-
-    ids_dev = torch.randint(0, vocab, (total_seqs, seq), device=dev)
-    host_ids = [torch.randint(0, vocab, (total_seqs, seq)).pin_memory() for _ in range(4)]
-    # the stock module keeps fp32 [b, heads, S, S] attention tensors: try the library's fused attention at the
-    # product's microbatch size first, then the eager module at the largest microbatch that fits
-    chosen = None
-    for attn, micro in (("sdpa", args.micro_batch or 4), ("flash_attention_2", args.micro_batch or 4), ("eager", 2),
-                        ("eager", 1)):
-        try:
-            model, opt, one_step, nmb = build(attn, micro)
-            for _ in range(max(args.warmup, 1)):
-                one_step(ids_dev)
-            chosen = (attn, micro)
-            break
-        except Exception as e:                                   # noqa: BLE001 - OOM or unsupported attention
-            print(f"[baseline] attn={attn} micro={micro} failed: {type(e).__name__}: {str(e)[:120]}", file=sys.stderr)
-            model = opt = one_step = None
-            import gc
-            gc.collect()
-            torch.cuda.empty_cache()
-    if chosen is None:
-        print(json.dumps({"impl": "baseline", "unavailable": "stock HF GPT-J 6B does not fit in fp32-master mode"}))
-        return 0
-    micro = chosen[1]
-    torch.cuda.synchronize()
-    sampler = ClockSampler(0)
-    sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        one_step(ids_dev)
-    e1.record()
-    torch.cuda.synchronize()
-    ms_a = e0.elapsed_time(e1) / args.steps
-    e0.record()
-    last = None
-    for i in range(args.steps):
-        last = float(one_step(host_ids[i % 4].to(dev, non_blocking=True)).item())
-    e1.record()
-    torch.cuda.synchronize()
-    ms_b = e0.elapsed_time(e1) / args.steps
-    clocks = sampler.stop()
-    tokens = micro * nmb * seq
-    flops = train_flops_per_token(mcfg, seq)
-    print(json.dumps({
-        "metric": "training tokens/sec (device-timed, max over ranks), GPT-J-6B bf16 seq 2048",
-        "value": round(tokens / ms_a * 1e3, 1), "unit": "tokens/s", "n_gpus": 1, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": round(ms_a, 2), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "bf16 autocast, fp32 master", "data": "synthetic tokens, random-init weights",
-        "impl": "baseline-library (HF GPTJForCausalLM + cuBLAS + torch fused AdamW)",
-        "config": {"model": args.model, "params": param_count(mcfg), "layers": mcfg["num_layers"],
-                   "global_batch": micro * nmb, "seq_len": seq, "microbatches": nmb, "micro_batch": micro,
-                   "parallelism": "dp1", "attention": chosen[0], "valid": not bool(args.layers)},
-        "model_tflops_per_gpu": round(tokens / ms_a * 1e3 * flops / 1e12, 1), "clocks": clocks,
-        "e2e": {"value": round(tokens / ms_b * 1e3, 1), "unit": "tokens/s", "h2d_bytes_per_step": micro * nmb * seq * 8,
-                "d2h_bytes_per_step": 4, "ms_per_step": round(ms_b, 2), "last_loss": last},
-        "gpu_launches": 0, "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 1)}), flush=True)
-    return 0
-
-
 def pick_parallelism(n, spec):
     """Returns (pp, tp, sdp, label)."""
     import re
@@ -231,14 +131,19 @@ def pick_parallelism(n, spec):
     return pp, tp, sdp, spec
 
 
-def main():
-    args = parse()
-    if args.impl == "reference":
-        return reference_arm(args)
+def baseline_table():
+    """Tokens/s of the comparison arm (``--impl baseline``) measured on B200 this round, keyed
+    "model/N/parallelism"; written by hand from the logs under profiles/ (see BASELINE.md section 5)."""
+    path = os.path.join(ROOT, "baseline", "measured.json")
+    try:
+        with open(path) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return {}
 
-    if args.impl == "baseline" and int(os.environ.get("WORLD_SIZE", "1")) == 1 and args.model == "gpt-j-6b":
-        return library_baseline(args)
 
+def run_product(args, model_name, parallelism, steps, warmup, micro=0, nmb=0, checkpoint=-1, offload=0):
+    """One timed run of the library through its public API; returns the JSON line (rank 0) or None."""
     import torch
     import torch.distributed as dist
 
@@ -247,18 +152,15 @@ def main():
     from smdistributed_modelparallel_b200.ops import _native as N
 
     n = int(os.environ.get("WORLD_SIZE", "1"))
-    if n != args.gpus:
-        print(f"[bench] WORLD_SIZE={n} but --gpus {args.gpus}; using WORLD_SIZE", file=sys.stderr)
-    pp, tp, sdp, label = pick_parallelism(n, args.parallelism)
+    pp, tp, sdp, label = pick_parallelism(n, parallelism)
     dp = n // (pp * tp)
-    mcfg = dict(MODEL_CONFIGS[args.model])
+    mcfg = dict(MODEL_CONFIGS[model_name])
     if args.layers:
         mcfg["num_layers"] = args.layers
     seq = args.seq or mcfg["num_positions"]
     # per-N batch geometry (weak scaling: sequences per step grow with N)
-    micro = args.micro_batch or 4
-    nmb = args.microbatches or (2 if pp == 1 else 8)
-    baseline = args.impl == "baseline"
+    micro = micro or args.micro_batch or 4
+    nmb = nmb or args.microbatches or (2 if pp == 1 else 8)
 
     half = torch.float16 if args.fp16 else torch.bfloat16
     conf = {"microbatches": nmb, "bf16": not args.fp16, "fp16": bool(args.fp16),
@@ -268,13 +170,13 @@ def main():
         conf["sharded_data_parallel_degree"] = sdp
     if pp > 1:      # pipeline window: microbatches in flight on the leader (memory vs. overlap; 4 measured best at pp2)
         conf["active_microbatches"] = args.active_microbatches or min(4, nmb)
-    if args.offload:
+    if offload:
         conf["offload_activations"] = True
     if tp > 1:
         conf["prescaled_batch"] = False
+    if os.environ.get("BENCH_TP_COMM") == "nccl":
+        conf["fused_tp_collectives"] = False       # ablation: NCCL collectives next to the library's own GEMMs
     os.environ.setdefault("SMP_LOG_LEVEL", "warning")
-    if baseline or os.environ.get("BENCH_TP_COMM") == "nccl":
-        conf["fused_tp_collectives"] = False       # NCCL collectives next to the GEMMs (the comparison arm)
     smp.init(conf)
     from smdistributed_modelparallel_b200.parallel import tp_ops
     dev = torch.device("cuda", smp.local_rank())
@@ -282,7 +184,7 @@ def main():
 
     with smp.model_creation(tensor_parallelism=tp > 1, dtype=half):
         module = smp.nn.DistributedTransformerLMHead(**mcfg)
-    use_ckpt = args.checkpoint if args.checkpoint >= 0 else (1 if args.model == "gpt-neox-20b" else 0)
+    use_ckpt = checkpoint if checkpoint >= 0 else (args.checkpoint if args.checkpoint >= 0 else (1 if model_name == "gpt-neox-20b" else 0))
     if use_ckpt:
         smp.set_activation_checkpointing(module.transformer.seq_layers, pack_args_as_tuple=True, strategy="each")
     model = smp.DistributedModel(module)
@@ -316,9 +218,10 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 1)):
+    for _ in range(max(warmup, 1)):
         one_step(dev_ids)
     sync_all()
+    torch.cuda.reset_peak_memory_stats()
 
     sampler = ClockSampler(smp.local_rank())
     if smp.rank() == 0:
@@ -328,32 +231,32 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         out = one_step(dev_ids)
     e1.record()
     sync_all()
-    ms_a = e0.elapsed_time(e1) / args.steps
+    ms_a = e0.elapsed_time(e1) / steps
     launches = N.launches()
     # ---- phase B: end to end (pinned host ids -> device every step, loss read back every step)
     sync_all()
     t0 = time.perf_counter()
     e0.record()
     last = None
-    for i in range(args.steps):
+    for i in range(steps):
         ids = host_ids[i % len(host_ids)].to(dev, non_blocking=True)
         out = one_step(ids)
         last = float(out.reduce_mean().item())
     e1.record()
     sync_all()
-    ms_b = e0.elapsed_time(e1) / args.steps
-    wall_b = (time.perf_counter() - t0) * 1000 / args.steps
+    ms_b = e0.elapsed_time(e1) / steps
+    wall_b = (time.perf_counter() - t0) * 1000 / steps
     clocks = sampler.stop() if smp.rank() == 0 else None
 
     if os.environ.get("BENCH_TORCH_PROFILE"):
-        # diagnosis only (after the timed regions): one step under torch.profiler, chrome trace per rank
+        # diagnosis only (after the timed regions): one step under torch.profiler, summarised per rank on the box
         from torch.profiler import ProfilerActivity, profile
         sync_all()
-        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
             one_step(dev_ids)
             sync_all()
         os.makedirs(os.environ["BENCH_TORCH_PROFILE"], exist_ok=True)
@@ -363,32 +266,86 @@ def main():
     if n > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_a, ms_b = float(t[0]), float(t[1])
+    peak = torch.cuda.max_memory_allocated() / 2 ** 30
+    line = None
     if smp.rank() == 0:
         value = tokens_per_step / (ms_a / 1000)
         e2e = tokens_per_step / (ms_b / 1000)
-        flops = train_flops_per_token(mcfg, seq) * (4.0 / 3.0 if use_ckpt else 1.0)
+        flops = train_flops_per_token(mcfg, seq)                  # model FLOPs: recomputation is not counted
+        base = baseline_table().get(f"{model_name}/{n}/{label}")
         line = {
-            "metric": f"training tokens/sec (device-timed, max over ranks), {METRIC_NAMES.get(args.model, args.model)} {'fp16' if args.fp16 else 'bf16'} seq {seq}",
-            "value": round(value, 1), "unit": "tokens/s", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": round(ms_a, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "metric": f"training tokens/sec (device-timed, max over ranks), {METRIC_NAMES.get(model_name, model_name)} {'fp16' if args.fp16 else 'bf16'} seq {seq}",
+            "value": round(value, 1), "unit": "tokens/s", "n_gpus": n, "steps": steps, "warmup": warmup,
+            "ms_per_step": round(ms_a, 2), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": round(value / base, 3) if base else None,
             "dtype": "fp16" if args.fp16 else "bf16", "data": "synthetic tokens, random-init weights",
-            "impl": "baseline-nccl-cublas" if baseline else "b200",
-            "config": {"model": args.model, "params": param_count(mcfg), "layers": mcfg["num_layers"],
+            "impl": "b200",
+            "config": {"model": model_name, "params": param_count(mcfg), "layers": mcfg["num_layers"],
                        "global_batch": global_batch, "seq_len": seq, "microbatches": nmb, "micro_batch": micro,
-                       "parallelism": label, "tp_comm": tp_ops.get_comm_mode() if tp > 1 else None, "activation_checkpointing": bool(use_ckpt), "offload_activations": bool(args.offload),
+                       "parallelism": label, "tp_comm": tp_ops.get_comm_mode() if tp > 1 else None, "activation_checkpointing": bool(use_ckpt), "offload_activations": bool(offload),
                        "active_microbatches": conf.get("active_microbatches", nmb) if pp > 1 else None,
                        "optimizer": "AdamW fp32 master" + (", state sharded over dp" if args.shard_optimizer_state else ""),
                        "l2": f"working set ({2 * param_count(mcfg) / 2 ** 30:.1f} GiB of 16-bit weights read per pass) >> 126 MB L2; no explicit flush needed",
+                       "baseline_tokens_per_s": base,
                        "valid": not bool(args.layers)},
             "model_tflops_per_gpu": round(value * flops / n / 1e12, 1),
+            "model_tflops_note": "6 x matmul params + full (non-causal) attention products per token; the kernels skip the masked half of causal attention",
             "clocks": clocks,
             "e2e": {"value": round(e2e, 1), "unit": "tokens/s", "h2d_bytes_per_step": per_rank_batch * seq * 8,
                     "d2h_bytes_per_step": 4 * nmb, "ms_per_step": round(ms_b, 2), "last_loss": last},
             "gpu_launches": launches,
-            "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 1),
+            "peak_mem_gb": round(peak, 1),
         }
-        print(json.dumps(line), flush=True)
     sync_all()
+    # leave the process ready for another configuration
+    del model, optimizer, module, train_step
+    smp.reset()
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    return line
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    if args.impl == "baseline":
+        from baseline.engine import run as run_baseline
+        from smdistributed_modelparallel_b200.models.configs import MODEL_CONFIGS, param_count, train_flops_per_token
+
+        mcfg = dict(MODEL_CONFIGS[args.model])
+        if args.layers:
+            mcfg["num_layers"] = args.layers
+        line = run_baseline(args, mcfg, ClockSampler, train_flops_per_token, param_count)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return 0
+
+    n = int(os.environ.get("WORLD_SIZE", "1"))
+    if n != args.gpus:
+        print(f"[bench] WORLD_SIZE={n} but --gpus {args.gpus}; using WORLD_SIZE", file=sys.stderr)
+    line = run_product(args, args.model, args.parallelism, args.steps, args.warmup, checkpoint=args.checkpoint,
+                       offload=args.offload)
+    # BASELINE.json's headline metric has two halves: GPT-J 6B PPxTP (the line above) and GPT-NeoX 20B under sharded data
+    # parallelism with activation checkpointing + offload on 8 GPUs; the second rides along as "secondary"
+    second = None
+    spec = os.environ.get("BENCH_SECONDARY", "1")        # "0": off; "model,parallelism,ckpt,offload": override (tests)
+    sec = ("gpt-neox-20b", "sdp8", 1, 1) if (n == 8 and args.model == "gpt-j-6b" and not args.parallelism and spec == "1") else None
+    if spec not in ("0", "1"):
+        f = spec.split(",")
+        sec = (f[0], f[1], int(f[2]), int(f[3]))
+    if sec is not None:
+        k2 = max(3, min(args.steps, int(os.environ.get("BENCH_SECONDARY_STEPS", "8"))))
+        try:
+            second = run_product(args, sec[0], sec[1], k2, min(args.warmup, 3), checkpoint=sec[2], offload=sec[3])
+        except Exception as e:                                   # noqa: BLE001 - the headline line must still print
+            second = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
+    if line is not None:
+        if second is not None:
+            line["secondary"] = second
+        print(json.dumps(line), flush=True)
     return 0
 
 

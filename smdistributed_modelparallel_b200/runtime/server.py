@@ -29,6 +29,7 @@ What is different (by design):
 
 from __future__ import annotations
 
+import contextlib
 import os
 import threading
 import traceback
@@ -130,6 +131,15 @@ class PipelineP2P:
         self._seen, self._cursor, self._posted = {}, {}, {}
         self.lookahead = max(1, int(os.environ.get("SMP_STATIC_LOOKAHEAD", "2")))
         self.stats = {"recorded_steps": 0, "replayed_steps": 0, "preposted": 0}
+        # Receives are posted from a dedicated stream: ProcessGroupNCCL orders a point-to-point call after
+        # everything already enqueued on the stream it is issued from, and the host runs far ahead of the GPU, so a
+        # receive posted from the compute stream would not start (and would keep the sender's kernel spinning)
+        # until all queued compute had drained.  The buffer is allocated on that stream too and handed to the
+        # compute stream (event wait + record_stream) only when its consumer runs.
+        self._recv_stream = None
+        dev = getattr(state, "device", None)
+        if dev is not None and dev.type == "cuda" and os.environ.get("SMP_P2P_SIDE_STREAM", "1") != "0":
+            self._recv_stream = torch.cuda.Stream(device=dev)
 
     def _wire(self, t):
         t = t.detach()
@@ -182,7 +192,11 @@ class PipelineP2P:
 
         def finish():
             for w in works:
-                w.wait()
+                w.wait()                    # NCCL: the current stream waits for the transfer; gloo / host: blocks
+            if self._recv_stream is not None:
+                cur = torch.cuda.current_stream(device)
+                for b in out:
+                    b.record_stream(cur)    # allocated on the receive stream, consumed on this one
             return [b.to(torch.bool) if dt == torch.bool else b for b, (_, dt) in zip(out, metas)]
 
         return finish if defer else finish()
@@ -191,15 +205,18 @@ class PipelineP2P:
         host = self._via_host(src, self.me)
         group = None if host else self.state.pp_p2p_groups[(src, self.me)]
         out, works = [], []
-        for shape, dtype in metas:
-            wire_dtype = torch.uint8 if dtype == torch.bool else dtype
-            buf = torch.empty(shape, dtype=wire_dtype, device=device)
-            if host:
-                works.append(_HostRecv(self.state.comm, src, self._next_host_tx(src, self.me), buf))
-                self.host_stats["received"] += 1
-            else:
-                works.append(dist.irecv(buf, src=src, group=group))
-            out.append(buf)
+        side = self._recv_stream if (not host and self._recv_stream is not None) else None
+        ctx = torch.cuda.stream(side) if side is not None else contextlib.nullcontext()
+        with ctx:
+            for shape, dtype in metas:
+                wire_dtype = torch.uint8 if dtype == torch.bool else dtype
+                buf = torch.empty(shape, dtype=wire_dtype, device=device)
+                if host:
+                    works.append(_HostRecv(self.state.comm, src, self._next_host_tx(src, self.me), buf))
+                    self.host_stats["received"] += 1
+                else:
+                    works.append(dist.irecv(buf, src=src, group=group))
+                out.append(buf)
         return out, works
 
     # ------------------------------------------------------------------ static mode
@@ -863,17 +880,22 @@ class ExecutionServer:
                 raise
             finally:
                 self._step_ctx = None
-            wire = map_structure(lambda x: x.cpu() if torch.is_tensor(x) else x, outputs)
+            # the outputs go to the other stages as tensor stubs + point-to-point transfers (no device-to-host copy,
+            # so the leader's host does not wait for the step's GPU work before it can start the next step)
+            skel, tensors = stubify(outputs)
             for r in group:
                 if r != self.me:
-                    self.comm.server_send(StepDone(self._step, wire), r)
+                    self.comm.server_send(StepDone(self._step, skel), r)
+                    self.p2p.send(tensors, r)
         else:
             while self._done_msg is None:
                 self._pump_one(50)
             if self._done_msg.error is not None:
                 raise SMPRuntimeError(f"the step failed on pipeline rank 0: {self._done_msg.error}")
-            dev = st.device
-            outputs = map_structure(lambda x: x.to(dev) if torch.is_tensor(x) else x, self._done_msg.outputs)
+            skel = self._done_msg.outputs
+            metas = [(sb.shape, sb.dtype) for sb in stubs_of(skel)]
+            leader = self.core.pp_rank_to_rank(0)
+            outputs = destubify(skel, self.p2p.recv(metas, leader, st.device))
         self.p2p.drain()
         self.records.clear()
         self.boundaries.clear()
