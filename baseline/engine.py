@@ -43,7 +43,8 @@ class _Masters:
                 m.grad = torch.empty_like(m)
         torch._foreach_copy_([m.grad for m in self.masters], grads)          # 16-bit grads -> fp32 master grads
         self.opt.step()
-        torch._foreach_copy_(self.params, self.masters)                     # masters -> 16-bit model weights
+        with torch.no_grad():
+            torch._foreach_copy_(self.params, self.masters)                 # masters -> 16-bit model weights
 
 
 def _groups(n, pp, tp):

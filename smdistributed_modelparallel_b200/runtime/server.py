@@ -131,14 +131,15 @@ class PipelineP2P:
         self._seen, self._cursor, self._posted = {}, {}, {}
         self.lookahead = max(1, int(os.environ.get("SMP_STATIC_LOOKAHEAD", "2")))
         self.stats = {"recorded_steps": 0, "replayed_steps": 0, "preposted": 0}
-        # Receives are posted from a dedicated stream: ProcessGroupNCCL orders a point-to-point call after
-        # everything already enqueued on the stream it is issued from, and the host runs far ahead of the GPU, so a
-        # receive posted from the compute stream would not start (and would keep the sender's kernel spinning)
-        # until all queued compute had drained.  The buffer is allocated on that stream too and handed to the
-        # compute stream (event wait + record_stream) only when its consumer runs.
+        # A receive is ordered after the compute already enqueued on the current stream (ProcessGroupNCCL semantics),
+        # i.e. it starts when its consumer is about to run.  Posting it from a dedicated stream instead lets it start
+        # at once - measured on 2 x B200 (GPT-J 6B pp2, profiles/pp2_p2p_variants.log) that is much slower (33.3k vs
+        # 44.3k tokens/s): an NCCL receive kernel that waits for its sender spins on the GPU for the whole wait and
+        # holds up work of other streams queued behind it on the same hardware connection.  So the side stream is
+        # an opt-in (SMP_P2P_SIDE_STREAM=1) for platforms where early posting pays.
         self._recv_stream = None
         dev = getattr(state, "device", None)
-        if dev is not None and dev.type == "cuda" and os.environ.get("SMP_P2P_SIDE_STREAM", "1") != "0":
+        if dev is not None and dev.type == "cuda" and os.environ.get("SMP_P2P_SIDE_STREAM", "0") == "1":
             self._recv_stream = torch.cuda.Stream(device=dev)
 
     def _wire(self, t):
