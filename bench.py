@@ -170,6 +170,9 @@ def run_product(args, model_name, parallelism, steps, warmup, micro=0, nmb=0, ch
         conf["sharded_data_parallel_degree"] = sdp
     if pp > 1:      # pipeline window: microbatches in flight on the leader (memory vs. overlap; 4 measured best at pp2)
         conf["active_microbatches"] = args.active_microbatches or min(4, nmb)
+        # balance the stages by time, not by parameter bytes: 180 GB per GPU leaves memory to spare here, and the
+        # embedding table would otherwise count like several (tensor-parallel) layers
+        conf["memory_weight"] = float(os.environ.get("BENCH_MEMORY_WEIGHT", "0.0"))
     if offload:
         conf["offload_activations"] = True
     if tp > 1:
@@ -284,6 +287,7 @@ def run_product(args, model_name, parallelism, steps, warmup, micro=0, nmb=0, ch
                        "global_batch": global_batch, "seq_len": seq, "microbatches": nmb, "micro_batch": micro,
                        "parallelism": label, "tp_comm": tp_ops.get_comm_mode() if tp > 1 else None, "activation_checkpointing": bool(use_ckpt), "offload_activations": bool(offload),
                        "active_microbatches": conf.get("active_microbatches", nmb) if pp > 1 else None,
+                       "memory_weight": conf.get("memory_weight") if pp > 1 else None,
                        "optimizer": "AdamW fp32 master" + (", state sharded over dp" if args.shard_optimizer_state else ""),
                        "l2": f"working set ({2 * param_count(mcfg) / 2 ** 30:.1f} GiB of 16-bit weights read per pass) >> 126 MB L2; no explicit flush needed",
                        "baseline_tokens_per_s": base,

@@ -87,11 +87,29 @@ def get_segments(costs, k: int, base_loads=None):
     return seg
 
 
+def estimated_work(m: nn.Module, tp_size: int = 1) -> float:
+    """Stand-in for a module's own execution time when no trace exists (delayed parameter initialisation, or
+    tracing switched off): the weights its GEMMs multiply, per tensor-parallel rank.  A tensor-parallel shard counts as
+    it is; a replicated weight is applied to this rank's 1/t of the tokens, so it counts 1/t; embedding tables are
+    looked up, not multiplied, and cost nothing.  (The reference always traces, torch/patches/tracing.py:41-86; its
+    fallback is parameter volume, which puts a 200 M-row embedding on a par with four sharded transformer layers.)"""
+    if isinstance(m, nn.Embedding) or type(m).__name__ in ("DistributedEmbedding",):
+        return 0.0
+    total = 0.0
+    for p in m.parameters(recurse=False):
+        if p.dim() < 2:
+            continue
+        sharded = getattr(p, "_smp_dist_axis", None) is not None
+        total += float(p.numel()) / (1.0 if sharded else float(max(1, tp_size)))
+    return total
+
+
 class ModulePartitioner:
     def __init__(self, root: nn.Module, num_partitions: int, memory_weight: float = 0.8, module_times=None,
-                 module_memory=None, manual=None, name_of=None):
+                 module_memory=None, manual=None, name_of=None, tp_size: int = 1):
         self.root_module = root
         self.k = num_partitions
+        self.tp_size = int(tp_size)
         self.w = float(memory_weight)
         self.times = module_times or {}
         self.memory = module_memory or {}
@@ -111,22 +129,25 @@ class ModulePartitioner:
             seen.add(id(c))
             node.children.append(self._build(c, seen))
         node.sub_mem = node.own_mem + sum(c.sub_mem for c in node.children)
+        node.sub_work = estimated_work(m, self.tp_size) + sum(c.sub_work for c in node.children)
         if m in self.times:
             node.sub_time = float(self.times[m])
         else:
             node.sub_time = None
         return node
 
-    def _fill_costs(self, node, total_mem, total_time):
+    def _fill_costs(self, node, total_mem, total_time, total_work=0.0):
         for c in node.children:
-            self._fill_costs(c, total_mem, total_time)
+            self._fill_costs(c, total_mem, total_time, total_work)
         mem = node.sub_mem / total_mem if total_mem > 0 else 0.0
         if total_time and node.sub_time is not None:
             t = node.sub_time / total_time
         elif total_time:
             t = sum((c.sub_time or 0.0) for c in node.children) / total_time
+        elif total_work > 0:
+            t = node.sub_work / total_work      # no trace: time estimated from the GEMM weights (estimated_work)
         else:
-            t = mem                   # no trace: time taken proportional to parameter volume
+            t = mem
         node.cost = self.w * mem + (1.0 - self.w) * t
         node.own_cost = max(0.0, node.cost - sum(c.cost for c in node.children))
 
@@ -195,7 +216,7 @@ class ModulePartitioner:
         seen = {id(self.root_module)}
         root = self._build(self.root_module, seen)
         total_time = root.sub_time if root.sub_time else 0.0
-        self._fill_costs(root, root.sub_mem, total_time)
+        self._fill_costs(root, root.sub_mem, total_time, root.sub_work)
         out = {}
         self._place(root, list(range(self.k)), out)
         self._colocate_shared_parameters(out)
@@ -237,7 +258,8 @@ def partition_model(model_root: nn.Module, module_manager, cfg, module_times=Non
         walk(model_root, default, assignment)
     else:
         part = ModulePartitioner(model_root, pp, cfg.memory_weight, module_times, module_memory,
-                                 manual=module_manager.manual_partition_of, name_of=module_manager.get_module_name)
+                                 manual=module_manager.manual_partition_of, name_of=module_manager.get_module_name,
+                                 tp_size=cfg.tensor_parallel_degree)
         assignment = part.partition()
     if len(list(model_root.modules())) < pp:
         raise ModelTooSmallError()

@@ -87,3 +87,28 @@ def test_shared_parameters_are_colocated():
     model = Tied()
     assign = ModulePartitioner(model, 2, memory_weight=1.0).partition()
     assert assign[model.emb] == assign[model.out]
+
+
+def test_untraced_time_estimate_ignores_embedding_tables():
+    """Without a trace (delayed parameter initialisation) the time half of the cost comes from the GEMM weights: an
+    embedding table is a lookup and must not weigh like layers, and a replicated output projection counts 1/tp."""
+    import torch.nn as nn
+
+    from smdistributed_modelparallel_b200.pipeline.partition import ModulePartitioner, estimated_work
+
+    class LM(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = nn.Embedding(4096, 64)                      # 262k parameters, no GEMM
+            self.layers = nn.Sequential(*[nn.Linear(64, 64, bias=False) for _ in range(16)])   # 4k each
+            self.head = nn.Linear(64, 128, bias=False)             # 8k = two layers' worth
+
+    m = LM()
+    assert estimated_work(m.emb) == 0.0 and estimated_work(m.head, tp_size=4) == 64 * 128 / 4
+    # time-weighted: 16 + 2 units split 9 / 9 -> the stage holding the embedding still gets ~9 layers
+    assign = ModulePartitioner(m, 2, memory_weight=0.0).partition()
+    n0 = sum(1 for l in m.layers if assign[l] == 0)
+    assert 8 <= n0 <= 10, n0
+    # memory-weighted (the reference's fallback): the embedding table pushes almost every layer to the other stage
+    assign = ModulePartitioner(m, 2, memory_weight=1.0).partition()
+    assert sum(1 for l in m.layers if assign[l] == assign[m.emb]) <= 2
