@@ -136,7 +136,7 @@ class Runner:
         H = self.cfg["hidden_size"]
         act_shape = (micro * self.tp, self.seq, H)
         warm = min(self.pp - 1 - self.pr, nmb)
-        inputs, outputs = [], []
+        inputs, outputs, pending = [], [], []
 
         def fwd(i):
             x_in = None
@@ -146,7 +146,9 @@ class Runner:
                 x_in.requires_grad_(True)
             out = self._fwd_stage(chunks[i], x_in)
             if self.next is not None:
-                dist.send(out.detach(), dst=self.next)
+                # asynchronous: in the steady state this stage sends an activation forward while the next stage sends
+                # a gradient back, and two blocking sends facing each other never complete
+                pending.append((dist.isend(out.detach(), dst=self.next), out))
             inputs.append(x_in)
             outputs.append(out)
 
@@ -162,7 +164,7 @@ class Runner:
                     out.backward()
                     total.add_(out.detach())
             if self.prev is not None:
-                dist.send(x_in.grad, dst=self.prev)
+                pending.append((dist.isend(x_in.grad, dst=self.prev), x_in.grad))
 
         for i in range(warm):
             fwd(i)
@@ -174,6 +176,8 @@ class Runner:
         while done < nmb:
             bwd(done == nmb - 1)
             done += 1
+        for work, _keep in pending:
+            work.wait()
         opt.step()
         return total
 

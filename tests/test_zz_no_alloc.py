@@ -70,9 +70,11 @@ def test_static_scratch_colsum_matches_on_two_consecutive_calls():
         assert torch.isfinite(got).all()
         rel = ((got - ref).norm() / (ref.norm() + 1e-12)).item()
         assert rel < 1e-5, f"static-scratch colsum differs from caller-scratch colsum: rel {rel:.3e}"
-        oracle = x.float().sum(0)
-        rel = ((got - oracle).norm() / (oracle.norm() + 1e-12)).item()
-        assert rel < 1e-2, f"colsum differs from the fp32 oracle: rel {rel:.3e}"
+        # independent oracle: the same sum in float64 on the 16-/32-bit inputs as stored (both kernels accumulate in
+        # fp32, so only summation order separates them from it)
+        oracle = x.double().sum(0)
+        rel = ((got.double() - oracle).norm() / (oracle.norm() + 1e-12)).item()
+        assert rel < 2e-6, f"colsum differs from the float64 oracle: rel {rel:.3e}"
 
 
 def test_static_scratch_colsum_rejects_oversize():
