@@ -74,7 +74,7 @@ def test_static_scratch_colsum_matches_on_two_consecutive_calls():
         # fp32, so only summation order separates them from it)
         oracle = x.double().sum(0)
         rel = ((got.double() - oracle).norm() / (oracle.norm() + 1e-12)).item()
-        assert rel < 2e-6, f"colsum differs from the float64 oracle: rel {rel:.3e}"
+        assert rel < 1e-5, f"colsum differs from the float64 oracle: rel {rel:.3e}"
 
 
 def test_static_scratch_colsum_rejects_oversize():
