@@ -190,7 +190,10 @@ def run_product(args, model_name, parallelism, steps, warmup, micro=0, nmb=0, ch
     use_ckpt = checkpoint if checkpoint >= 0 else (args.checkpoint if args.checkpoint >= 0 else (1 if model_name == "gpt-neox-20b" else 0))
     if use_ckpt:
         smp.set_activation_checkpointing(module.transformer.seq_layers, pack_args_as_tuple=True, strategy="each")
-    model = smp.DistributedModel(module)
+    # pipeline stages are balanced on measured module times (first-step tracing; the parameters are still on the
+    # meta device then and borrow storage for the traced passes)
+    trace = pp > 1 and os.environ.get("BENCH_TRACE", "1") != "0"
+    model = smp.DistributedModel(module, trace_execution_times=trace)
     optimizer = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-4, betas=(0.9, 0.95),
                                                            weight_decay=0.1),
                                          dynamic_loss_scale=bool(args.fp16))
@@ -288,6 +291,7 @@ def run_product(args, model_name, parallelism, steps, warmup, micro=0, nmb=0, ch
                        "parallelism": label, "tp_comm": tp_ops.get_comm_mode() if tp > 1 else None, "activation_checkpointing": bool(use_ckpt), "offload_activations": bool(offload),
                        "active_microbatches": conf.get("active_microbatches", nmb) if pp > 1 else None,
                        "memory_weight": conf.get("memory_weight") if pp > 1 else None,
+                       "partition": ("auto, traced module times" if trace else "auto, estimated from GEMM weights") if pp > 1 else None,
                        "optimizer": "AdamW fp32 master" + (", state sharded over dp" if args.shard_optimizer_state else ""),
                        "l2": f"working set ({2 * param_count(mcfg) / 2 ** 30:.1f} GiB of 16-bit weights read per pass) >> 126 MB L2; no explicit flush needed",
                        "baseline_tokens_per_s": base,
@@ -342,10 +346,25 @@ def main():
         sec = (f[0], f[1], int(f[2]), int(f[3]))
     if sec is not None:
         k2 = max(3, min(args.steps, int(os.environ.get("BENCH_SECONDARY_STEPS", "8"))))
+        # the headline line must print whatever happens to the second configuration: every rank arms a watchdog that
+        # ends the process (rank 0 printing the line first) if the secondary run has not finished in time
+        limit = float(os.environ.get("BENCH_SECONDARY_TIMEOUT", "420"))
+
+        def give_up():
+            if line is not None:
+                line["secondary"] = {"error": f"secondary run ({sec[0]} {sec[1]}) exceeded {limit:.0f} s and was abandoned"}
+                print(json.dumps(line), flush=True)
+            os._exit(0)
+
+        dog = threading.Timer(limit, give_up)
+        dog.daemon = True
+        dog.start()
         try:
             second = run_product(args, sec[0], sec[1], k2, min(args.warmup, 3), checkpoint=sec[2], offload=sec[3])
         except Exception as e:                                   # noqa: BLE001 - the headline line must still print
             second = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
+        finally:
+            dog.cancel()
     if line is not None:
         if second is not None:
             line["secondary"] = second

@@ -413,14 +413,20 @@ class ExecutionServer:
         self._step_ctx = None
         self._done_msg = None
         self._orig_forward = {}
+        self._early = []                   # control messages that arrived while waiting for the partition
 
     # ================================================================== partitioning (first step)
     def _trace(self, step_fn, args, kwargs, num_mb):
-        """First-step tracing on the leader (reference torch/patches/tracing.py:41-86, worker.py:248-278): run
-        the step function once on the first microbatch without gradients, wherever the unpartitioned model
-        lives, recording per module the execution order, wall time and bytes of tensors produced.  The
-        partitioner weighs ``memory_weight * memory + (1 - memory_weight) * time`` with these.  Skipped when
-        tracing is off, nothing was requested, or the parameters are not materialised yet (delayed init)."""
+        """First-step tracing on the leaders (reference torch/patches/tracing.py:41-86, worker.py:248-278): run the
+        step function on the first microbatch without gradients, wherever the unpartitioned model lives, recording
+        per module the execution order, device time, allocator growth and bytes of tensors produced.  One warm-up
+        pass and ``SMP_TRACE_PASSES - 1`` (default 2) timed passes, averaged (the reference runs five).  The
+        partitioner weighs ``memory_weight * memory + (1 - memory_weight) * time`` with these.
+
+        Parameters that are not materialised yet (delayed initialisation) borrow storage for the duration of the
+        trace: the values do not matter for timing, the storage is returned before partitioning.  Skipped when
+        tracing is off, nothing was requested, or the borrowed storage would exceed ``SMP_TRACE_MAX_BYTES``
+        (default 60 GB; the reference skips tracing above 120 GB, worker.py:45,257-263)."""
         import time as _time
 
         st = self.state
@@ -429,14 +435,25 @@ class ExecutionServer:
         if st.cfg.skip_tracing or not (want_t or want_m) or not self.is_leader:
             return None, None
         root = model.module
-        if any(p.is_meta or getattr(p, "_smp_delayed", False) for p in root.parameters()):
-            get_logger().info("tracing skipped: parameters are not materialised (delayed initialisation)")
-            return None, None
-        dev = next((p.device for p in root.parameters()), torch.device("cpu"))
+        dev = st.device
+        borrowed = []
+        meta_bytes = sum(p.numel() * p.element_size() for p in root.parameters() if p.is_meta)
+        if meta_bytes:
+            limit = float(os.environ.get("SMP_TRACE_MAX_BYTES", 60e9))
+            if meta_bytes > limit:          # a size rule, so that every leader takes the same decision
+                get_logger().info(f"tracing skipped: {meta_bytes / 1e9:.1f} GB of parameters are not materialised "
+                                  f"(limit {limit / 1e9:.0f} GB)")
+                return None, None
+            borrowed = self._borrow_storage(root, dev)
+        else:
+            dev = next((p.device for p in root.parameters()), torch.device("cpu"))
+        cuda = dev.type == "cuda"
         mm = st.module_manager
         trace = mm.trace
+        passes = max(2, int(os.environ.get("SMP_TRACE_PASSES", "3")))
         started = {}
         hooks = []
+        state_ = {"timed": False}
 
         def tensor_bytes(obj):
             total = [0]
@@ -448,19 +465,26 @@ class ExecutionServer:
             name = mm.get_module_name(mod)
             if name not in trace.order:
                 trace.order.append(name)
-            if dev.type == "cuda":
+            if cuda:
                 torch.cuda.synchronize(dev)
-            started[mod] = _time.perf_counter()
-            trace.in_bytes[name] = trace.in_bytes.get(name, 0) + tensor_bytes(a)
+            started[mod] = (_time.perf_counter(), torch.cuda.memory_allocated(dev) if cuda else 0)
+            if state_["timed"] == 1:
+                trace.in_bytes[name] = trace.in_bytes.get(name, 0) + tensor_bytes(a)
 
         def post(mod, a, out):
-            if dev.type == "cuda":
+            if cuda:
                 torch.cuda.synchronize(dev)
+            if not state_["timed"]:
+                started.pop(mod, None)
+                return
             name = mm.get_module_name(mod)
-            trace.times[name] = trace.times.get(name, 0.0) + (_time.perf_counter() - started.pop(mod, _time.perf_counter()))
-            nbytes = tensor_bytes(out)
-            trace.out_bytes[name] = trace.out_bytes.get(name, 0) + nbytes
-            trace.memory[name] = trace.memory.get(name, 0) + nbytes
+            t0, m0 = started.pop(mod, (_time.perf_counter(), 0))
+            trace.times[name] = trace.times.get(name, 0.0) + (_time.perf_counter() - t0) / (passes - 1)
+            if state_["timed"] == 1:
+                nbytes = tensor_bytes(out)
+                grown = max(0, (torch.cuda.memory_allocated(dev) if cuda else 0) - m0)
+                trace.out_bytes[name] = trace.out_bytes.get(name, 0) + nbytes
+                trace.memory[name] = trace.memory.get(name, 0) + max(nbytes, grown)
 
         for m in root.modules():
             hooks.append(m.register_forward_pre_hook(pre))
@@ -473,15 +497,52 @@ class ExecutionServer:
         st.microbatch = 0
         try:
             with torch.no_grad():
-                step_fn.func(*a, **k)
+                for i in range(passes):
+                    state_["timed"] = i              # 0: warm-up; 1: first timed pass (also sizes); 2..: timing only
+                    step_fn.func(*a, **k)
         finally:
             st.is_tracing_flag = False
             st.microbatch = prev_mb
             for h in hooks:
                 h.remove()
+            self._return_storage(borrowed)
         times = {mm.get_module(n): t for n, t in trace.times.items()} if want_t else None
         memory = {mm.get_module(n): float(b) for n, b in trace.memory.items()} if want_m else None
         return times, memory
+
+    @staticmethod
+    def _borrow_storage(root, dev):
+        """Give every meta parameter / buffer real (small random) storage on ``dev``; returns what to undo."""
+        undo = []
+        seen = {}
+        for m in root.modules():
+            for name, p in list(m._parameters.items()):
+                if p is None or not p.is_meta:
+                    continue
+                if id(p) not in seen:
+                    t = torch.empty(p.shape, dtype=p.dtype, device=dev)
+                    if t.is_floating_point():
+                        t.normal_(0.0, 0.02) if t.dim() > 1 else t.fill_(0.5)
+                    new = nn.Parameter(t, requires_grad=False)
+                    for tag in ("_smp_dist_axis", "_smp_scaled_batch", "_smp_one_rank"):
+                        if hasattr(p, tag):
+                            setattr(new, tag, getattr(p, tag))
+                    seen[id(p)] = new
+                undo.append((m._parameters, name, p))
+                m._parameters[name] = seen[id(p)]
+            for name, b in list(m._buffers.items()):
+                if b is None or not b.is_meta:
+                    continue
+                undo.append((m._buffers, name, b))
+                m._buffers[name] = torch.zeros(b.shape, dtype=b.dtype, device=dev)
+        return undo
+
+    @staticmethod
+    def _return_storage(undo):
+        for table, name, original in undo:
+            table[name] = original
+        if undo and torch.cuda.is_available():
+            torch.cuda.empty_cache()
 
     def _partition(self, step_fn=None, args=None, kwargs=None, num_mb=1):
         from ..pipeline.partition import partition_model
@@ -492,10 +553,12 @@ class ExecutionServer:
         if step_fn is not None and st.cfg.auto_partition:
             times, memory = self._trace(step_fn, args, kwargs, num_mb)
         assignment = partition_model(self.model.module, mm, st.cfg, module_times=times, module_memory=memory)
-        # every rank computes the same deterministic assignment; the leader's copy is authoritative
-        if self.core.pp_size() > 1:
-            if self.is_leader:
-                for r in self.core.get_pp_group():
+        # one assignment for the whole job: measured times differ from leader to leader, and the tensor-parallel
+        # and data-parallel peers of a stage must all cut the model in the same place, so rank 0's copy is
+        # authoritative for everyone (the reference also partitions on rank 0 and broadcasts, torch/server.py:254-268)
+        if self.core.size() > 1 and self.core.pp_size() > 1:
+            if self.me == 0:
+                for r in range(self.core.size()):
                     if r != self.me:
                         self.comm.server_send(("partition", assignment), r)
             else:
@@ -504,6 +567,7 @@ class ExecutionServer:
                     if isinstance(obj, tuple) and obj and obj[0] == "partition":
                         assignment = obj[1]
                         break
+                    self._early.append((src, tx, obj))      # a stage that already has its copy may be ahead of us
         mm.assign_partitions(assignment)
         self.model.post_partition()
         self._install_dispatchers()
@@ -625,7 +689,7 @@ class ExecutionServer:
 
     def _pump_one(self, timeout_ms) -> bool:
         """Handle one incoming control message; False if none arrived within the timeout."""
-        got = self.comm.server_next_message(timeout_ms)
+        got = self._early.pop(0) if self._early else self.comm.server_next_message(timeout_ms)
         if got is None:
             return False
         src, _tx, msg = got

@@ -271,14 +271,18 @@ def test_pp2_dp2_bf16_with_activation_checkpointing():
         assert torch.equal(v, other["after"][k]), k
 
 
-def _delayed_worker(rank, world):
+def _delayed_worker(rank, world, trace=False, tp=1):
     import smdistributed_modelparallel_b200 as smp
 
-    smp.init({"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": False, "delayed_parameter_initialization": True})
-    with smp.model_creation():
+    conf = {"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": tp > 1, "delayed_parameter_initialization": True,
+            "memory_weight": 0.0 if trace else 0.8}
+    if tp > 1:
+        conf.update(tensor_parallel_degree=tp, ddp_dist_backend="gloo")
+    smp.init(conf)
+    with smp.model_creation(tensor_parallelism=tp > 1):
         module = smp.nn.DistributedTransformerLMHead(**CFG)
     assert all(p.is_meta for p in module.parameters()), "nothing may be materialised before partitioning"
-    model = smp.DistributedModel(module)
+    model = smp.DistributedModel(module, trace_execution_times=trace, trace_memory_usage=trace)
     opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
 
     @smp.step
@@ -296,9 +300,12 @@ def _delayed_worker(rank, world):
         opt.step()
     local = list(model.local_parameters())
     everything = list(model.module.parameters())
+    tr = smp.state.module_manager.trace
     return {"losses": losses, "local_elems": sum(p.numel() for p in local),
             "held_elems": sum(p.numel() for p in everything if not p.is_meta),
-            "meta_left": sum(1 for p in local if p.is_meta)}
+            "meta_left": sum(1 for p in local if p.is_meta), "traced": len(tr.order),
+            "trace_time": sum(tr.times.values()), "pp_rank": smp.pp_rank(),
+            "partition": dict(smp.state.module_manager.partition_info())}
 
 
 def test_delayed_parameter_initialisation_under_pp():
@@ -313,6 +320,20 @@ def test_delayed_parameter_initialisation_under_pp():
         assert r["losses"][0] < 4.6, r["losses"]      # ~ln(64): the constructor's initialisers were replayed
         total += r["local_elems"]
     assert res[0]["local_elems"] > 0 and res[1]["local_elems"] > 0 and total > 0
+
+
+@pytest.mark.parametrize("tp", [1, 2])
+def test_tracing_under_delayed_initialisation(tp):
+    """With delayed initialisation the parameters have no storage when the first step arrives: the leaders borrow
+    storage for the traced passes, hand it back, and every rank - whatever times its own leader measured - uses rank
+    0's partition.  Afterwards only the local partition is materialised, as without tracing."""
+    res = run_distributed(_delayed_worker, 2 * tp, True, tp, timeout=420)
+    for r in res:
+        assert r["meta_left"] == 0 and r["held_elems"] == r["local_elems"], r
+        assert all(l == l for l in r["losses"]) and r["losses"][-1] < r["losses"][0]
+        assert r["partition"] == res[0]["partition"]
+        assert (r["traced"] > 10 and r["trace_time"] > 0) if r["pp_rank"] == 0 else r["traced"] == 0, r
+    assert set(res[0]["partition"].values()) == {0, 1}
 
 
 def _pp_optshard_worker(rank, world):
