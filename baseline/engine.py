@@ -30,7 +30,7 @@ class _Masters:
     def __init__(self, params, lr, betas, wd):
         self.params = [p for p in params if p.requires_grad]
         self.masters = [p.detach().float().clone().requires_grad_(True) for p in self.params]
-        self.opt = torch.optim.AdamW(self.masters, lr=lr, betas=betas, weight_decay=wd, fused=True)
+        self.opt = torch.optim.AdamW(self.masters, lr=lr, betas=betas, weight_decay=wd, fused=self.masters[0].is_cuda)
 
     def zero_grad(self):
         for p in self.params:
@@ -66,19 +66,38 @@ def _groups(n, pp, tp):
                 g = dist.new_group(ranks) if dp > 1 else None
                 if a == pr and c == tr:
                     dp_group = g
-    return pr, dr, tr, dp, tp_group, dp_group
+    # one 2-rank group per direction between neighbouring stages: activations going forward and gradients coming back
+    # are ordered independently (on one communicator, "send a1" on one side and "send g0" on the other wait for each
+    # other's next receive)
+    fwd_groups, bwd_groups = {}, {}
+    if n > 1 and pp > 1:
+        stage = dp * tp
+        for a in range(pp - 1):
+            for i in range(stage):
+                pair = [a * stage + i, (a + 1) * stage + i]
+                f, b = dist.new_group(pair), dist.new_group(pair)
+                if rank in pair:
+                    fwd_groups[tuple(pair)] = f
+                    bwd_groups[tuple(pair)] = b
+    return pr, dr, tr, dp, tp_group, dp_group, fwd_groups, bwd_groups
 
 
 class Runner:
-    def __init__(self, args, mcfg, n):
+    def __init__(self, args, mcfg, n, device=None, dtype=torch.bfloat16):
         self.args, self.cfg, self.n = args, mcfg, n
         pp, tp, sdp, self.label = parse_parallelism(n, args.parallelism)
         self.pp, self.tp, self.sdp = pp, tp, sdp
         self.local = int(os.environ.get("LOCAL_RANK", "0"))
-        self.dev = torch.device("cuda", self.local)
-        torch.cuda.set_device(self.dev)
-        if n > 1 and not dist.is_initialized():
-            dist.init_process_group("nccl", device_id=self.dev)
+        self.dtype = dtype
+        if device is not None and torch.device(device).type == "cpu":      # plumbing tests (gloo)
+            self.dev = torch.device("cpu")
+            if n > 1 and not dist.is_initialized():
+                dist.init_process_group("gloo")
+        else:
+            self.dev = torch.device("cuda", self.local)
+            torch.cuda.set_device(self.dev)
+            if n > 1 and not dist.is_initialized():
+                dist.init_process_group("nccl", device_id=self.dev)
         self.rank = dist.get_rank() if n > 1 else 0
         self.seq = args.seq or mcfg["num_positions"]
         self.micro = args.micro_batch or 4
@@ -94,17 +113,17 @@ class Runner:
     # ---- pp x tp x dp
     def _build_mp(self):
         n, pp, tp = self.n, self.pp, self.tp
-        self.pr, self.dr, self.tr, self.dp, self.tp_group, self.dp_group = _groups(n, pp, tp)
+        self.pr, self.dr, self.tr, self.dp, self.tp_group, self.dp_group, self.fwd_g, self.bwd_g = _groups(n, pp, tp)
         L = self.cfg["num_layers"]
         per = (L + pp - 1) // pp
         lo, hi = self.pr * per, min(L, (self.pr + 1) * per)
-        self.model = RefGPT(self.cfg, self.tp_group, torch.bfloat16, self.dev, (lo, hi), first=self.pr == 0,
+        self.model = RefGPT(self.cfg, self.tp_group, self.dtype, self.dev, (lo, hi), first=self.pr == 0,
                             last=self.pr == pp - 1)
         self.model.ckpt = self.ckpt
         self.ddp = None
         if self.dp > 1:
             from torch.nn.parallel import DistributedDataParallel as DDP
-            self.ddp = DDP(self.model, device_ids=[self.local], process_group=self.dp_group, bucket_cap_mb=100,
+            self.ddp = DDP(self.model, device_ids=[self.local] if self.dev.type == "cuda" else None, process_group=self.dp_group, bucket_cap_mb=100,
                            gradient_as_bucket_view=True)
         self.opt = _Masters(self.model.parameters(), 1e-4, (0.9, 0.95), 0.1)
         self.prev = None if self.pr == 0 else self.rank - self.dp * tp
@@ -141,14 +160,14 @@ class Runner:
         def fwd(i):
             x_in = None
             if self.prev is not None:
-                x_in = torch.empty(act_shape, dtype=torch.bfloat16, device=self.dev)
-                dist.recv(x_in, src=self.prev)
+                x_in = torch.empty(act_shape, dtype=self.dtype, device=self.dev)
+                dist.recv(x_in, src=self.prev, group=self.fwd_g[(self.prev, self.rank)])
                 x_in.requires_grad_(True)
             out = self._fwd_stage(chunks[i], x_in)
             if self.next is not None:
                 # asynchronous: in the steady state this stage sends an activation forward while the next stage sends
                 # a gradient back, and two blocking sends facing each other never complete
-                pending.append((dist.isend(out.detach(), dst=self.next), out))
+                pending.append((dist.isend(out.detach(), dst=self.next, group=self.fwd_g[(self.rank, self.next)]), out))
             inputs.append(x_in)
             outputs.append(out)
 
@@ -157,14 +176,14 @@ class Runner:
             sync = contextlib.nullcontext() if (self.ddp is None or last_mb) else self.ddp.no_sync()
             with sync:
                 if self.next is not None:
-                    g = torch.empty(act_shape, dtype=torch.bfloat16, device=self.dev)
-                    dist.recv(g, src=self.next)
+                    g = torch.empty(act_shape, dtype=self.dtype, device=self.dev)
+                    dist.recv(g, src=self.next, group=self.bwd_g[(self.rank, self.next)])
                     out.backward(g)
                 else:
                     out.backward()
                     total.add_(out.detach())
             if self.prev is not None:
-                pending.append((dist.isend(x_in.grad, dst=self.prev), x_in.grad))
+                pending.append((dist.isend(x_in.grad, dst=self.prev, group=self.bwd_g[(self.prev, self.rank)]), x_in.grad))
 
         for i in range(warm):
             fwd(i)
