@@ -52,6 +52,54 @@ def vit_translator(config=None):
 
 
 def t5_block_init_hook(config, has_relative_attention_bias=False, *args, **kwargs):
+    """``T5Block(config, has_relative_attention_bias)`` -> DistributedTransformerLayer arguments (reference
+    torch/nn/huggingface/t5.py:11-33).  The block that owns the relative-attention-bias table (the first of each
+    stack) stays a HuggingFace module: returning None tells the registry not to distribute it."""
     if has_relative_attention_bias:
-        raise HFT5ConfigError("T5 blocks that own the relative position bias cannot be distributed")
-    return None
+        return None
+    if config.d_kv * config.num_heads != config.d_model:
+        raise HFT5ConfigError(f"d_kv ({config.d_kv}) x num_heads ({config.num_heads}) must equal d_model "
+                              f"({config.d_model}) for a distributed T5 block")
+    return (), dict(num_attention_heads=config.num_heads, attention_head_size=config.d_kv,
+                    hidden_size=config.d_model, intermediate_size=config.d_ff,
+                    attention_dropout_prob=config.dropout_rate, hidden_dropout_prob=config.dropout_rate,
+                    add_cross_attention=bool(config.is_decoder))
+
+
+def _bias_plus_mask(position_bias, mask):
+    """HuggingFace hands every block the relative position bias [1|B, heads, Sq, Sk] and an additive mask
+    [B, 1, 1|Sq, Sk]; the distributed layer takes their sum as one additive per-head bias (the layer keeps this
+    rank's heads).  Unlike the reference (t5.py:62-72, which adds in place and so stacks the mask onto the shared bias
+    again at every layer), the sum is a new tensor."""
+    if position_bias is None:
+        return mask
+    return position_bias if mask is None else position_bias + mask
+
+
+def t5_block_forward_hook(hidden_states, attention_mask=None, position_bias=None, encoder_hidden_states=None,
+                          encoder_attention_mask=None, encoder_decoder_position_bias=None, layer_head_mask=None,
+                          cross_attn_layer_head_mask=None, past_key_value=None, use_cache=False,
+                          output_attentions=False, return_dict=True, **extra):
+    """T5Block.forward arguments -> the distributed layer's input tuple (reference t5.py:35-98)."""
+    past = past_key_value if past_key_value is not None else extra.get("past_key_values")
+    head_masks = (layer_head_mask, cross_attn_layer_head_mask, extra.get("encoder_layer_head_mask"))
+    if any(m is not None for m in head_masks) or past is not None or use_cache or output_attentions:
+        raise HFT5ConfigError("head masks, cached keys / values, use_cache and output_attentions are not supported by "
+                              "the distributed T5 block")
+    if attention_mask is None and position_bias is None:
+        raise HFT5ConfigError("attention_mask is a required argument of the distributed T5 block")
+    self_mask = _bias_plus_mask(position_bias, attention_mask)
+    if encoder_hidden_states is not None:
+        cross_mask = _bias_plus_mask(encoder_decoder_position_bias, encoder_attention_mask)
+        return ((hidden_states, self_mask, encoder_hidden_states, cross_mask),), {}
+    return ((hidden_states, self_mask),), {}
+
+
+def t5_block_return_hook(outputs):
+    """The HuggingFace stack indexes a block's result as (hidden_states, position_bias[, cross position bias]); the
+    biases come from the undistributed first block, so later blocks return None for them (reference t5.py:100-101)."""
+    return (outputs[0], None, None)
+
+
+def get_t5_block_hooks():
+    return t5_block_init_hook, t5_block_forward_hook, t5_block_return_hook

@@ -218,6 +218,9 @@ class DistributedAttentionLayer(DistributedModule):
 
     def _attend(self, q, k, v, B, S, causal, attention_mask):
         d, la = self.attention_head_size, self.local_attention_size
+        bias = None
+        if isinstance(attention_mask, tuple):        # (boolean mask or None, additive per-head bias): see _full_mask
+            attention_mask, bias = attention_mask
         scale = 1.0 / math.sqrt(d) if self.scale_attention_scores else 1.0
         if self.scale_attn_by_layer_idx and not self.query_key_layer_scaling:
             scale = scale / float(self.layer_idx + 1)
@@ -232,7 +235,7 @@ class DistributedAttentionLayer(DistributedModule):
                 gemm_scale /= float(self.layer_idx + 1)
         ctx = A.core_attention(q, k, v, causal=causal, mask=mask, scale=scale, dropout_p=self.attention_dropout_prob,
                                training=self.training, window=self.window_size if causal else None,
-                               gemm_scale=gemm_scale, token_major=True)
+                               gemm_scale=gemm_scale, token_major=True, bias=bias)
         return ctx.reshape(B * S, la)        # [B, S, heads, d] straight from the attention kernel
 
     def forward(self, inp):
@@ -283,6 +286,16 @@ def _full_mask(attention_mask, full_batch, group):
     if attention_mask is None:
         return None
     m = attention_mask
+    if m.dim() == 4 and m.is_floating_point() and m.shape[1] > 1:
+        # additive bias with a head dimension (the reference's T5 hooks add the relative position bias to the mask,
+        # torch/nn/huggingface/t5.py:62-82): this rank's heads, kept additive; entries at or below -1e4 also mask
+        heads = m.shape[1]
+        local = get_local_channels(heads)
+        start = sum(get_local_channels(heads, r) for r in range(tp_rank()))
+        b_local = m.narrow(1, start, local)
+        if group is not None and b_local.shape[0] not in (1, full_batch):
+            b_local = tp_ops.gather_tokens(b_local.contiguous(), group)
+        return (None, b_local)
     if m.dim() == 2:
         m = (m == 0)
     else:

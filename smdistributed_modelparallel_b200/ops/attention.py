@@ -222,7 +222,7 @@ def _dropout_counter():
 # --------------------------------------------------------------------------------- core attention
 def core_attention(q, k, v, *, causal: bool = True, mask=None, scale: float | None = None, dropout_p: float = 0.0,
                    training: bool = True, window: int | None = None, gemm_scale: float = 1.0,
-                   token_major: bool = False):
+                   token_major: bool = False, bias=None):
     """softmax(scale * q k^T + mask) v for q,k,v [B, heads, S, d]; returns [B, heads, Sq, d], or [B, Sq, heads, d]
     with ``token_major``.
 
@@ -231,7 +231,8 @@ def core_attention(q, k, v, *, causal: bool = True, mask=None, scale: float | No
     ``window`` visible keys (local attention).  ``gemm_scale`` is accepted for the reference's
     ``query_key_layer_scaling`` / ``attention_in_fp32`` options (reference torch/nn/transformer.py:1769-1835): their
     purpose - keeping 16-bit scores in range - is moot here because scores only exist as fp32 accumulators in
-    tensor memory, so it does not change the result.
+    tensor memory, so it does not change the result.  ``bias`` is an additive score bias; calls that carry one run on the
+    library's scaled-dot-product attention instead of the fused kernels.
     """
     B, h, Sq, d = q.shape
     Sk = k.shape[2]
@@ -241,7 +242,7 @@ def core_attention(q, k, v, *, causal: bool = True, mask=None, scale: float | No
         mask = mask.to(torch.uint8) if mask.dtype != torch.uint8 else mask
         if mask.dim() != 4 or mask.stride(-1) != 1:
             mask = mask.reshape(mask.shape[0], 1, -1, mask.shape[-1]).contiguous()
-    if flash_applicable(q, k, v):
+    if bias is None and flash_applicable(q, k, v):
         seed, offset = _dropout_counter() if p_drop > 0.0 else (0, 0)
         return _FlashAttention.apply(q, k, v, mask, float(scale), bool(causal), int(window or 0), p_drop, seed, offset,
                                      token_major)
@@ -257,6 +258,10 @@ def core_attention(q, k, v, *, causal: bool = True, mask=None, scale: float | No
     if mask is not None:
         dead = mask.bool() if dead is None else (dead | mask.bool())
     keep = None if dead is None else ~dead
+    if bias is not None:
+        # additive score bias ([B|1, heads|1, Sq, Sk], e.g. T5's relative position bias): only the library path takes one
+        add = bias.to(q.dtype)
+        keep = add if dead is None else add.masked_fill(dead, float("-inf"))
     out = torch.nn.functional.scaled_dot_product_attention(q, k, v, attn_mask=keep, dropout_p=p_drop, scale=scale)
     if keep is not None:
         out = torch.nan_to_num(out, nan=0.0)            # rows without a visible key

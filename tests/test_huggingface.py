@@ -158,3 +158,60 @@ def test_vit_encoder_hooks_registered_by_hand():
     back = tr.smp_to_hf(model.state_dict())
     for k, v in sd.items():
         assert k in back and torch.equal(back[k], v), k
+
+
+def test_t5_block_hooks_and_additive_position_bias():
+    """T5 hooks (reference torch/nn/huggingface/t5.py): the bias-owning first block is left alone, later blocks map to
+    DistributedTransformerLayer; position bias + additive mask travel as one per-head additive bias, which the
+    attention op honours (library path) - checked against the explicit softmax."""
+    import math
+
+    import pytest
+    import torch
+    from transformers import T5Config
+
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200.backend.exceptions import HFT5ConfigError
+    from smdistributed_modelparallel_b200.nn.huggingface import vit_t5
+    from smdistributed_modelparallel_b200.ops import attention as A
+
+    smp.init({"microbatches": 1})
+    cfg = T5Config(d_model=32, d_kv=8, num_heads=4, d_ff=64, dropout_rate=0.0, num_layers=2)
+    init, fwd, ret = vit_t5.get_t5_block_hooks()
+    assert init(cfg, has_relative_attention_bias=True) is None
+    _, kw = init(cfg, has_relative_attention_bias=False)
+    assert kw["num_attention_heads"] == 4 and kw["attention_head_size"] == 8 and kw["intermediate_size"] == 64
+    assert kw["add_cross_attention"] is False
+    with pytest.raises(HFT5ConfigError):
+        init(T5Config(d_model=32, d_kv=16, num_heads=4, d_ff=64), has_relative_attention_bias=False)
+
+    torch.manual_seed(0)
+    B, S = 2, 6
+    hidden = torch.randn(B, S, 32)
+    mask = torch.zeros(B, 1, 1, S)
+    mask[1, :, :, -2:] = -1e9
+    bias = torch.randn(1, 4, S, S)
+    (inp,), _ = fwd(hidden, attention_mask=mask, position_bias=bias)
+    assert torch.equal(inp[1], bias + mask) and inp[1] is not bias and torch.equal(bias, bias.clone())
+    with pytest.raises(HFT5ConfigError):
+        fwd(hidden, attention_mask=mask, use_cache=True)
+    (inp2,), _ = fwd(hidden, attention_mask=mask, position_bias=bias, encoder_hidden_states=torch.randn(B, 5, 32),
+                     encoder_attention_mask=torch.zeros(B, 1, 1, 5))
+    assert len(inp2) == 4 and inp2[2].shape == (B, 5, 32)
+    assert ret((hidden, "x"))[1:] == (None, None)
+
+    # the attention op with an additive per-head bias
+    q, k, v = [torch.randn(B, 4, S, 8) for _ in range(3)]
+    got = A.core_attention(q, k, v, causal=False, scale=1.0, bias=bias + mask)
+    ref = torch.softmax(q @ k.transpose(-1, -2) + bias + mask, dim=-1) @ v
+    assert torch.allclose(got, ref, atol=1e-5)
+
+    # and through a distributed layer: the bias changes the result, masked keys stay masked
+    layer = smp.nn.DistributedTransformerLayer(**kw)
+    out_b, _ = layer((hidden, bias + mask))
+    out_0, _ = layer((hidden, mask))
+    assert out_b.shape == hidden.shape and not torch.allclose(out_b, out_0)
+    hidden2 = hidden.clone()
+    hidden2[1, -1] += 10.0                     # a masked key position of sample 1 ...
+    out_c, _ = layer((hidden2, bias + mask))
+    assert torch.allclose(out_c[1, :-2], out_b[1, :-2], atol=1e-5)      # ... cannot influence the visible queries
