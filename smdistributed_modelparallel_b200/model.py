@@ -86,6 +86,7 @@ class DistributedModel(nn.Module):
         self.sdp_engine = None
         self._partitioned = False
         self._num_steps = 0
+        self._join = None
 
         # 1. precision
         self.dtype = torch.float16 if cfg.fp16 else (torch.bfloat16 if cfg.bf16 else None)
@@ -265,6 +266,11 @@ class DistributedModel(nn.Module):
         (reference model.py:1154-1235)."""
         self._backward_passes += 1
         sync = (self._backward_passes % self.backward_passes_per_step) == 0
+        if getattr(self, "_join", None) is not None and sync and torch.is_grad_enabled():
+            active = self._join_count(1)                 # joined ranks answer with 0 from _join_drain
+            self._join["steps"] += 1
+            if self.reducer is not None:
+                self.reducer.scale_override = None if self._join["by_world"] else 1.0 / max(active, 1)
         if self.reducer is not None:
             self.reducer.require_sync = sync
             if sync:
@@ -518,10 +524,78 @@ class DistributedModel(nn.Module):
             self.reducer.register_comm_hook(hook_state, hook)
 
     @contextmanager
-    def join(self, divide_by_initial_world_size=True, enable=True):
-        """Uneven-input context.  Microbatch counts are fixed per step here, so ranks never diverge inside a
-        step; the context is accepted for API compatibility (reference ddp_model.py:652-775)."""
-        yield
+    def join(self, divide_by_initial_world_size=True, enable=True, throw_on_early_termination=False):
+        """Training with a different number of steps per data-parallel rank (reference torch/ddp_model.py:652-775, the
+        adaptation of ``DistributedDataParallel.join`` to its reducers; on PyTorch >= 1.10 the reference refuses).
+
+        Inside the context every synchronising step first counts the ranks still training.  A rank that leaves the
+        context keeps answering that count and shadows the others' gradient reductions with zeros until nobody is
+        left, then every rank takes the parameters and buffers of the rank that trained longest.  Gradients are
+        averaged over all ranks (``divide_by_initial_world_size``) or over the ranks still training.  While the
+        context is active the reduction is not overlapped with backward.  Plain data parallelism only."""
+        if not enable or state.core.dp_size() == 1:
+            yield
+            return
+        cfg = state.cfg
+        if (state.core.pp_size() > 1 or state.core.tp_size() > 1 or self.sdp_engine is not None
+                or cfg.shard_optimizer_state or cfg._fp32_grad_accumulation):
+            raise SMPUnsupportedError("join supports plain data parallelism only (no pipeline / tensor / sharded "
+                                      "data parallelism, optimizer-state sharding or fp32 gradient accumulation)")
+        if self.reducer is not None and self.reducer.comm_hook is not None:
+            raise SMPUnsupportedError("join cannot be combined with a communication hook")
+        group = state.dp_process_group
+        self._join = {"group": group, "by_world": bool(divide_by_initial_world_size), "steps": 0,
+                      "throw": bool(throw_on_early_termination)}
+        if self.reducer is not None:
+            self.reducer.joining = True
+        failed = False
+        try:
+            yield
+        except BaseException:
+            failed = True                # the other ranks cannot be answered consistently any more
+            raise
+        finally:
+            ctx, self._join = self._join, None
+            if self.reducer is not None:
+                self.reducer.joining = False
+                self.reducer.scale_override = None
+            if not failed:
+                self._join_drain(ctx)
+
+    def _join_count(self, active: int) -> int:
+        t = torch.tensor([float(active)], device=state.device)
+        dist.all_reduce(t, group=self._join["group"] if self._join else None)
+        return int(t.item())
+
+    def _join_drain(self, ctx):
+        """After leaving ``join``: shadow the remaining ranks' steps, then adopt the final model."""
+        group = ctx["group"]
+        self._join = ctx
+        try:
+            while True:
+                if self._join_count(0) == 0:
+                    break
+                if ctx["throw"]:
+                    raise RuntimeError("join: another rank is still training after this rank ran out of inputs")
+                if self._partitioned and self.reducer is not None:
+                    self.reducer.shadow_synchronize()
+        finally:
+            self._join = None
+        # the rank that trained longest is authoritative (ties: lowest rank)
+        me = dist.get_rank(group)
+        key = torch.tensor([float(ctx["steps"]) * 4096.0 + (4095.0 - me)], device=state.device)
+        dist.all_reduce(key, op=dist.ReduceOp.MAX, group=group)
+        src_in_group = 4095 - int(key.item()) % 4096
+        src = dist.get_global_rank(group, src_in_group)
+        with torch.no_grad():
+            for t in list(self.module.parameters()) + list(self.module.buffers()):
+                if not t.is_meta:
+                    dist.broadcast(t.data, src=src, group=group)
+            # 16-bit training: the fp32 master weights must follow, or the next step would restore the old values
+            b16 = getattr(state.optimizer, "fp16_optimizer", None) if state.optimizer is not None else None
+            for grp in (getattr(b16, "fp32_from_fp16_groups", None) or []):
+                for m in grp:
+                    dist.broadcast(m.data, src=src, group=group)
 
     # ------------------------------------------------------------------ state dict API
     def local_state_dict(self, destination=None, prefix="", keep_vars=False):

@@ -159,6 +159,11 @@ class GradReducer:
         self._hooks = []
         self.is_last_microbatch = lambda: True
         self.stats = {"overlapped_elems": 0, "tail_elems": 0}
+        # uneven inputs (DistributedModel.join): reductions run un-overlapped in a fixed order that a rank which has run
+        # out of data can reproduce with zero gradients; ``scale_override`` replaces 1 / dp_size when the average is
+        # taken over the ranks still training
+        self.joining = False
+        self.scale_override = None
 
     def register_comm_hook(self, state, hook):
         self.comm_hook = (state, hook)
@@ -275,7 +280,7 @@ class GradReducer:
             b["pending"], b["work"], b["flat"], b["dirty"] = len(b["params"]), None, None, False
 
     def _on_grad(self, p):
-        if getattr(self, "_gc", None) is None or not self.require_sync or self.comm_hook is not None:
+        if getattr(self, "_gc", None) is None or not self.require_sync or self.comm_hook is not None or self.joining:
             return
         mb = int(self._cur_mb())
         pid = self._param_id[p]
@@ -320,7 +325,7 @@ class GradReducer:
         return self.rdp_group if region == "scaled_batch" else self.dp_group
 
     def _bucket_ready(self, idx):
-        if not self.require_sync or not self.is_last_microbatch() or self.comm_hook is not None:
+        if not self.require_sync or not self.is_last_microbatch() or self.comm_hook is not None or self.joining:
             return
         buf = self.grad_buffer.buffer
         for region, a, b in self.buckets[idx]["ranges"]:
@@ -358,7 +363,7 @@ class GradReducer:
         group, both divided by the DP size (two reducers because tp shards see t x batch)."""
         if not self.require_sync or self.dp_size == 1:
             return
-        scale = 1.0 / self.dp_size
+        scale = 1.0 / self.dp_size if self.scale_override is None else float(self.scale_override)
         if self.grad_buffer is not None:
             if self.comm_hook is not None:
                 for region in ("scaled_batch", "default"):
@@ -371,6 +376,11 @@ class GradReducer:
             return
         done = self._finish_hook_overlap(scale) if getattr(self, "_gc", None) is not None else set()
         for want_scaled, group in ((True, self.rdp_group), (False, self.dp_group)):
+            if self.joining:
+                # fixed participation: every parameter, a missing gradient counting as zero (what a joined rank sends)
+                for p in self.params:
+                    if p.grad is None:
+                        p.grad = torch.zeros_like(p)
             grads = [p.grad for p in self.params
                      if p.grad is not None and p not in done and is_scaled_batch_parameter(p) == want_scaled]
             self.stats["tail_elems"] += sum(g.numel() for g in grads)
@@ -387,3 +397,24 @@ class GradReducer:
                 for g in gs:
                     g.copy_(flat[off:off + g.numel()].view_as(g))
                     off += g.numel()
+
+    def shadow_synchronize(self):
+        """A rank that has left ``DistributedModel.join`` takes part in the other ranks' gradient reduction with
+        zeros: the same collectives, in the same order, as ``synchronize`` issues while ``joining`` is set."""
+        if self.dp_size == 1:
+            return
+        if self.grad_buffer is not None:
+            self.grad_buffer.zero()
+        else:
+            for p in self.params:
+                p.grad = torch.zeros_like(p)
+        keep, self.require_sync, self.joining = self.require_sync, True, True
+        try:
+            self.synchronize()
+        finally:
+            self.require_sync = keep
+        if self.grad_buffer is not None:
+            self.grad_buffer.zero()
+        else:
+            for p in self.params:
+                p.grad = None

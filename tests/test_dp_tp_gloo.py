@@ -235,3 +235,45 @@ def test_tp2_rdp2_optimizer_state_sharding_matches_unsharded():
     sharded = run_distributed(_tp_optshard_worker, 4, True, timeout=300)
     assert plain[0]["losses"] == sharded[0]["losses"], (plain[0], sharded[0])
     assert plain[0]["virtual"] == 0 and sharded[0]["virtual"] >= 2
+
+
+def _join_worker(rank, world, by_world):
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.init({"microbatches": 2, "ddp": True, "ddp_dist_backend": "gloo"})
+    torch.manual_seed(3)
+    net = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.Tanh(), torch.nn.Linear(16, 4))
+    model = smp.DistributedModel(net)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.05))
+
+    @smp.step
+    def train_step(model, x, y):
+        loss = ((model(x) - y) ** 2).mean()
+        model.backward(loss)
+        return loss
+
+    steps = 2 if rank == 0 else 5                  # rank 0 runs out of data first
+    g = torch.Generator().manual_seed(10 + rank)
+    data = [(torch.randn(4, 8, generator=g), torch.randn(4, 4, generator=g)) for _ in range(steps)]
+    # oracle for the steps where only rank 1 still trains: its gradient divided by 2 (by_world) or by 1
+    with model.join(divide_by_initial_world_size=by_world):
+        for x, y in data:
+            opt.zero_grad()
+            train_step(model, x, y)
+            opt.step()
+    return {"params": [p.detach().clone() for p in model.parameters()], "steps": steps}
+
+
+@pytest.mark.parametrize("by_world", [True, False])
+def test_join_with_uneven_step_counts(by_world):
+    """DistributedModel.join: rank 0 stops after 2 steps, rank 1 after 5; nobody hangs, rank 0 shadows the remaining
+    reductions with zeros and both end with rank 1's parameters.  Dividing by the initial world size halves the
+    gradient of the lone steps; dividing by the active count does not - so the two settings must end differently."""
+    res = run_distributed(_join_worker, 2, by_world, timeout=300)
+    for a, b in zip(res[0]["params"], res[1]["params"]):
+        assert torch.equal(a, b)
+    test_join_with_uneven_step_counts.seen = getattr(test_join_with_uneven_step_counts, "seen", {})
+    test_join_with_uneven_step_counts.seen[by_world] = res[1]["params"]
+    seen = test_join_with_uneven_step_counts.seen
+    if len(seen) == 2:
+        assert any(not torch.equal(a, b) for a, b in zip(seen[True], seen[False]))
