@@ -43,6 +43,17 @@ class DistributedOptimizer:
         # known (pp > 1: at the first step, i.e. after this wrapper exists): remember every parameter's name so the
         # inner optimizer can be pointed at the real tensors then
         self._names_at_creation = {id(p): n for n, p in self.model.module.named_parameters(remove_duplicate=False)}
+        # index of every parameter in the optimizer as built over the whole (unpartitioned) model: the key space of
+        # full optimizer state dicts (optimizers/backcompat_opt.py)
+        self._global_index_to_name, self._global_group_indices = {}, []
+        idx = 0
+        for group in optimizer.param_groups:
+            ids = []
+            for p in group["params"]:
+                self._global_index_to_name[idx] = self._names_at_creation.get(id(p), f"param_{idx}")
+                ids.append(idx)
+                idx += 1
+            self._global_group_indices.append(ids)
         state.optimizer = self
         self.model._call_after_partitioning(self._after_partition)
         if state.loaded_optimizer_state is not None:
@@ -187,7 +198,22 @@ class DistributedOptimizer:
         return sd
 
     def load_state_dict(self, sd):
+        inner = sd.get("optimizer_state_dict", sd) if isinstance(sd, dict) else sd
+        if isinstance(inner, dict) and "_smp_param_names" in inner and "_smp_is_partial" not in inner:
+            from ..backend.exceptions import SMPValidationError
+            raise SMPValidationError("this is a full (gathered) optimizer state dict; load it with "
+                                     "load_state_dict_backcompat")
         self.load_optimizer_checkpoint_state(sd)
+
+    def state_dict_backcompat(self):
+        """Optimizer state gathered over the tensor- and pipeline-parallel ranks (deprecated full form; every rank of
+        the model-parallel group must call it)."""
+        from .backcompat_opt import full_state_dict
+        return full_state_dict(self)
+
+    def load_state_dict_backcompat(self, sd):
+        from .backcompat_opt import load_full_state_dict
+        return load_full_state_dict(self, sd)
 
     def local_optimizer_state_dict(self):
         """State of the parameters this rank updates, keyed like ``torch.optim.Optimizer.state_dict`` plus

@@ -277,3 +277,69 @@ def test_join_with_uneven_step_counts(by_world):
     seen = test_join_with_uneven_step_counts.seen
     if len(seen) == 2:
         assert any(not torch.equal(a, b) for a, b in zip(seen[True], seen[False]))
+
+
+def _full_opt_worker(rank, world, pp, tp):
+    import smdistributed_modelparallel_b200 as smp
+
+    CFG = dict(num_layers=4, num_attention_heads=4, attention_head_size=8, hidden_size=32, intermediate_size=64,
+               vocab_size=64, num_positions=16, attention_dropout_prob=0.0, hidden_dropout_prob=0.0,
+               embedding_dropout_prob=0.0, activation="gelu_new", causal_mask_size=16, pre_layernorm=True,
+               post_layernorm=False, final_layernorm=True, use_normal_initialization=True)
+    smp.init({"pipeline_parallel_degree": pp, "tensor_parallel_degree": tp, "microbatches": 2, "ddp": True,
+              "ddp_dist_backend": "gloo"})
+    torch.manual_seed(7)
+    with smp.tensor_parallelism(enabled=tp > 1):
+        module = smp.nn.DistributedTransformerLMHead(**CFG)
+    model = smp.DistributedModel(module)
+    opt = smp.DistributedOptimizer(torch.optim.Adam(model.parameters(), lr=1e-2))
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    torch.manual_seed(11)
+    ids = torch.randint(0, 64, (4, 16))
+    for _ in range(2):
+        opt.zero_grad()
+        train_step(model, ids)
+        opt.step()
+    full = opt.state_dict_backcompat()
+    want = {n: {k: (v.clone() if torch.is_tensor(v) else v) for k, v in opt.optimizer.state[p].items()}
+            for n, p in model.local_named_parameters() if p in opt.optimizer.state}
+    n_params_total = len(opt._global_index_to_name)
+    # refused by the ordinary loader, accepted by the back-compat one
+    refused = False
+    try:
+        opt.load_state_dict(full)
+    except Exception as e:                                  # noqa: BLE001
+        refused = "backcompat" in str(e)
+    for st in opt.optimizer.state.values():                 # wreck the state, then restore it from the full dict
+        for v in st.values():
+            if torch.is_tensor(v):
+                v.zero_()
+    loaded = opt.load_state_dict_backcompat(full)
+    worst = 0.0
+    for n, p in model.local_named_parameters():
+        if n in want:
+            for k, v in want[n].items():
+                if torch.is_tensor(v):
+                    worst = max(worst, (opt.optimizer.state[p][k].float() - v.float()).abs().max().item())
+    exp_avg_shapes = {full["_smp_param_names"][i]: tuple(st["exp_avg"].shape) for i, st in full["state"].items()}
+    return {"refused": refused, "loaded": loaded, "worst": worst, "n_full": len(full["state"]), "n_total": n_params_total,
+            "qkv_full_rows": exp_avg_shapes.get("transformer.seq_layers.0.attention.qkv_weight", (0,))[0],
+            "n_local": len(want)}
+
+
+@pytest.mark.parametrize("pp,tp", [(1, 2), (2, 2)])
+def test_full_optimizer_state_dict_round_trip(pp, tp):
+    """state_dict_backcompat / load_state_dict_backcompat (reference optimizers/backcompat_opt.py): the gathered
+    dictionary covers every parameter of the unpartitioned model with tensor-parallel tensors merged, the ordinary
+    loader refuses it, the back-compat loader restores exactly the local state."""
+    res = run_distributed(_full_opt_worker, pp * tp, pp, tp, timeout=420)
+    for r in res:
+        assert r["refused"] and r["worst"] == 0.0 and r["loaded"] == r["n_local"] > 0, r
+        assert r["n_full"] == r["n_total"], r
+        assert r["qkv_full_rows"] == 3 * 32, r               # both tp halves of the fused q/k/v rows
