@@ -61,12 +61,6 @@ def init(config=None):
 
     patch_manager.patch_constructor()
     state.tp_registry.register_builtin()
-    if cfg.optimize == "memory" and cfg.tensor_parallel_degree > 1:
-        # the reference's optimize=memory shards activations over the hidden dimension between GEMMs; the
-        # token-parallel layout used here for optimize=speed already keeps only 1/tp of every inter-GEMM
-        # activation, so both settings run the same code
-        get_logger().info("optimize='memory': activations are already sharded 1/tp by the token-parallel layout; "
-                          "running the same kernels as optimize='speed'")
     if torch.cuda.is_available():
         torch.cuda.set_device(core.local_rank())
     # tensor-parallel collectives: the fused peer-memory kernels are the default path on GPUs (they still check

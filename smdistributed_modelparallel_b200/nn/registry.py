@@ -155,4 +155,51 @@ class TensorParallelismRegistry:
         tf = self.translate_functions.get(cls)
         if tf is not None and tf not in self.active_translate_functions:
             self.active_translate_functions.append(tf)
+        if state.cfg._match_weights:
+            match_weights(module, dist_mod, tf[1] if tf is not None else None)
         return dist_mod
+
+
+def match_weights(module: nn.Module, dist_mod: nn.Module, hf_to_smp=None) -> int:
+    """``_match_weights`` (internal config key, reference torch/tp_registry.py:47-204,237-242): give the distributed
+    replacement the values of the module it replaces, so a test can compare the two numerically.  The reference copies
+    attribute by attribute with one routine per ``optimize`` mode; here the original's state dict goes through the
+    registered HuggingFace -> smp key translation and every entry is cut by the layout the distributed modules declare
+    (``state_dict_layout`` / the distribution-axis tags), which covers both layouts and uneven splits.  Returns the
+    number of tensors copied; modules that still sit on the meta device (delayed initialisation) are left alone."""
+    import torch
+
+    from ..checkpoint_utils import ONE_RANK, slice_for_rank
+    from .utils import is_distributed_parameter, is_one_rank_parameter, tp_rank, tp_size
+
+    sd = module.state_dict()
+    if any(torch.is_tensor(v) and v.is_meta for v in sd.values()):
+        return 0
+    if hf_to_smp is not None:
+        sd = hf_to_smp(dict(sd))
+    layout = {}
+    for mname, m in dist_mod.named_modules():
+        prefix = mname + "." if mname else ""
+        declared = getattr(m, "state_dict_layout", None)
+        if callable(declared):
+            layout.update({prefix + k: v for k, v in declared().items()})
+            continue
+        for pname, p in m.named_parameters(recurse=False):
+            if is_one_rank_parameter(p):
+                layout[prefix + pname] = (ONE_RANK, None)
+            elif is_distributed_parameter(p):
+                shapes = getattr(m, "weight_split_shapes", None)
+                layout[prefix + pname] = (p._smp_dist_axis, shapes.get(pname) if isinstance(shapes, dict) else shapes)
+    t, r = tp_size(), tp_rank()
+    own = dist_mod.state_dict()
+    picked = {}
+    for k, v in sd.items():
+        if k not in own or not torch.is_tensor(v):
+            continue
+        spec = layout.get(k)
+        if spec is not None and t > 1 and spec[0] != ONE_RANK:
+            v = slice_for_rank(v, spec, r, t)
+        if tuple(v.shape) == tuple(own[k].shape):
+            picked[k] = v
+    dist_mod.load_state_dict(picked, strict=False)
+    return len(picked)

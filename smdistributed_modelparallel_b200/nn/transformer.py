@@ -29,6 +29,7 @@ import torch.nn.functional as F
 
 from ..backend.exceptions import DistTransformerConfigError
 from ..ops import attention as A
+from ..ops import attention as A_ops
 from ..ops.cross_entropy import vocab_parallel_cross_entropy
 from ..parallel import tp_ops
 from .dist_module import DistributedModule, parse_args, update_copy_dict
@@ -55,6 +56,26 @@ def _param_dtype():
 
 def _group():
     return tp_group() if tp_size() > 1 else None
+
+
+def _memory_layout() -> bool:
+    """``optimize: memory`` (reference torch/nn/transformer.py:1429-1472,1519,1112,1138): between the GEMMs the
+    activations are ``[full batch, S, H / t]`` - every rank sees every token but only its slice of the hidden
+    dimension; q / k / v and the first MLP projection are partitioned along their *input* features and followed by a
+    reduce-scatter over the output features, LayerNorms are hidden-sharded (``DistributedLayerNorm``), and an all-to-all
+    converts from / to the ``[local batch, S, H]`` layout at the ends of a layer stack."""
+    s = _state()
+    return bool(getattr(s, "initialized", False) and s.cfg is not None and s.cfg.optimize == "memory" and tp_size() > 1)
+
+
+def _checkpoint_attentions() -> bool:
+    s = _state()
+    return bool(getattr(s, "initialized", False) and s.cfg is not None and s.cfg.checkpoint_attentions)
+
+
+def _plain_linear(x2, weight):
+    """x2 [rows, K] @ weight[N, K]^T on the library GEMM (autograd, wgrad into main_grad), no collective."""
+    return tp_ops.ColumnParallelLinear.apply(x2, weight, None, None, None, True)
 
 
 def _gelu_mode(activation: str):
@@ -99,6 +120,16 @@ class _NamedSlices:
 
 
 class DistributedAttentionLayer(DistributedModule):
+    """Self / cross attention block (reference torch/nn/transformer.py:1044-1420).
+
+    Keys that select between numerically equivalent implementations in the reference and have one implementation
+    here: ``fused_softmax`` (reference :1617-1657 chooses its softmax kernel or three torch ops; here the softmax
+    lives inside the attention kernel, csrc/kernels/sm100/attention.cu, whatever the flag says) and, on the MLP,
+    ``fused_bias_gelu`` (bias + GELU are the epilogue of the first GEMM).  ``mask_value`` is the finite number the
+    reference adds to masked scores; the kernel drops masked keys from the softmax exactly, which is the limit of
+    that as mask_value -> -inf and differs only for rows in which every key is masked (zero output here, the mean
+    of V there).  ``checkpoint_attentions`` is read in ``_attend``."""
+
     _KEYS = OrderedDict([
         ("num_attention_heads", 32), ("attention_head_size", 32), ("hidden_size", 1024),
         ("attention_dropout_prob", 0.1), ("hidden_dropout_prob", 0.1), ("layernorm_epsilon", 1e-5),
@@ -130,22 +161,41 @@ class DistributedAttentionLayer(DistributedModule):
         if self.rotary_dim is not None and self.rotary_emb_base is None:
             self.rotary_emb_base = 10000
         dtype = _param_dtype()
-        with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):
-            with initialize_with_output_partition(self):
-                self.qkv_weight = nn.Parameter(torch.empty(3 * la, H))
-                self.qkv_bias = nn.Parameter(torch.zeros(3 * la)) if self.use_qkv_bias else None
-            with initialize_with_input_partition(self, exclude_from_dist=["dense_bias"]):
-                self.dense_weight = nn.Parameter(torch.empty(H, la))
-                # the row-parallel bias lives on tp_rank 0 only and is added before the reduce-scatter
-                self.dense_bias = nn.Parameter(torch.zeros(H)) if (self.use_attn_dense_bias and tp_rank() == 0) else None
-            self._init_weights()
-        with parameter_creation_scope(self, scaled_batch=False, dtype=dtype):
-            mixed = bool(self.fp32_residual_addition)
-            self.pre_layernorm_mod = FusedLayerNorm(H, self.layernorm_epsilon, mixed_dtype=mixed) \
-                if self.pre_layernorm else None
-            self.layernorm = FusedLayerNorm(H, self.layernorm_epsilon) if self.post_layernorm else None
-        self.weight_split_shapes = {"qkv_weight": self.all_local_attention_sizes,
-                                    "dense_weight": self.all_local_attention_sizes}
+        self.memory_layout = _memory_layout()
+        self.hidden_split = [get_local_channels(H, r) for r in range(tp_size())]
+        Hl = get_local_channels(H)
+        if self.memory_layout:
+            A = self.num_attention_heads * d
+            with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):
+                with initialize_with_input_partition(self):
+                    self.qkv_weight = nn.Parameter(torch.empty(3 * A, Hl))      # every output feature, H/t inputs
+                    self.dense_weight = nn.Parameter(torch.empty(H, la))
+                with initialize_with_output_partition(self):
+                    self.qkv_bias = nn.Parameter(torch.zeros(3 * la)) if self.use_qkv_bias else None
+                    self.dense_bias = nn.Parameter(torch.zeros(Hl)) if self.use_attn_dense_bias else None
+                self._init_weights()
+            from .layer_norm import DistributedLayerNorm
+            with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):
+                self.pre_layernorm_mod = DistributedLayerNorm(H, self.layernorm_epsilon) if self.pre_layernorm else None
+                self.layernorm = DistributedLayerNorm(H, self.layernorm_epsilon) if self.post_layernorm else None
+            self.weight_split_shapes = {"qkv_weight": self.hidden_split, "dense_weight": self.all_local_attention_sizes}
+        else:
+            with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):
+                with initialize_with_output_partition(self):
+                    self.qkv_weight = nn.Parameter(torch.empty(3 * la, H))
+                    self.qkv_bias = nn.Parameter(torch.zeros(3 * la)) if self.use_qkv_bias else None
+                with initialize_with_input_partition(self, exclude_from_dist=["dense_bias"]):
+                    self.dense_weight = nn.Parameter(torch.empty(H, la))
+                    # the row-parallel bias lives on tp_rank 0 only and is added before the reduce-scatter
+                    self.dense_bias = nn.Parameter(torch.zeros(H)) if (self.use_attn_dense_bias and tp_rank() == 0) else None
+                self._init_weights()
+            with parameter_creation_scope(self, scaled_batch=False, dtype=dtype):
+                mixed = bool(self.fp32_residual_addition)
+                self.pre_layernorm_mod = FusedLayerNorm(H, self.layernorm_epsilon, mixed_dtype=mixed) \
+                    if self.pre_layernorm else None
+                self.layernorm = FusedLayerNorm(H, self.layernorm_epsilon) if self.post_layernorm else None
+            self.weight_split_shapes = {"qkv_weight": self.all_local_attention_sizes,
+                                        "dense_weight": self.all_local_attention_sizes}
         _NamedSlices.install(self, [("qkv_weight", "weight"), ("qkv_bias", "bias")], ("query", "key", "value"))
         self._install_name_hooks()
 
@@ -170,6 +220,13 @@ class DistributedAttentionLayer(DistributedModule):
 
     def state_dict_layout(self):
         sz = self.all_local_attention_sizes
+        if self.memory_layout:
+            hs = self.hidden_split
+            out = {f"{n}.weight": (1, hs) for n in ("query", "key", "value")}
+            out.update({f"{n}.bias": (0, sz) for n in ("query", "key", "value")})
+            out.update({"dense.weight": (1, sz), "dense.bias": (0, hs), "pre_layernorm.weight": (0, hs),
+                        "pre_layernorm.bias": (0, hs), "layernorm.weight": (0, hs), "layernorm.bias": (0, hs)})
+            return out
         out = {f"{n}.weight": (0, sz) for n in ("query", "key", "value")}
         out.update({f"{n}.bias": (0, sz) for n in ("query", "key", "value")})
         out["dense.weight"] = (1, sz)
@@ -188,8 +245,9 @@ class DistributedAttentionLayer(DistributedModule):
         else:
             # nn.Linear default (kaiming uniform with a=sqrt(5)) seen at full, unsplit size
             la, H = self.local_attention_size, self.hidden_size
+            blk = self.qkv_weight.shape[0] // 3
             for i in range(3):
-                nn.init.kaiming_uniform_(self.qkv_weight.data[i * la:(i + 1) * la], a=math.sqrt(5))
+                nn.init.kaiming_uniform_(self.qkv_weight.data[i * blk:(i + 1) * blk], a=math.sqrt(5))
             nn.init.kaiming_uniform_(self.dense_weight, a=math.sqrt(5))
             if self.qkv_bias is not None:
                 bound = 1.0 / math.sqrt(H)
@@ -233,9 +291,22 @@ class DistributedAttentionLayer(DistributedModule):
             gemm_scale = 1.0 / math.sqrt(d) if self.scale_attention_scores else 1.0
             if self.query_key_layer_scaling and self.scale_attn_by_layer_idx:
                 gemm_scale /= float(self.layer_idx + 1)
-        ctx = A.core_attention(q, k, v, causal=causal, mask=mask, scale=scale, dropout_p=self.attention_dropout_prob,
-                               training=self.training, window=self.window_size if causal else None,
-                               gemm_scale=gemm_scale, token_major=True, bias=bias)
+        def core(q, k, v):
+            return A.core_attention(q, k, v, causal=causal, mask=mask, scale=scale,
+                                    dropout_p=self.attention_dropout_prob, training=self.training,
+                                    window=self.window_size if causal else None, gemm_scale=gemm_scale,
+                                    token_major=True, bias=bias)
+
+        # checkpoint_attentions (reference torch/nn/transformer.py:1487-1493): do not keep the scores / probabilities
+        # for backward.  The fused kernel never stores them (it keeps q, k, v, the output and one log-sum-exp per
+        # row and recomputes the probabilities tile by tile), so the key only changes the library fallback, which
+        # would otherwise hold a [B, heads, Sq, Sk] tensor.
+        if _checkpoint_attentions() and torch.is_grad_enabled() and \
+                (bias is not None or not A.flash_applicable(q, k, v)) and (q.requires_grad or k.requires_grad):
+            from torch.utils.checkpoint import checkpoint
+            ctx = checkpoint(core, q, k, v, use_reentrant=False, preserve_rng_state=True)
+        else:
+            ctx = core(q, k, v)
         return ctx.reshape(B * S, la)        # [B, S, heads, d] straight from the attention kernel
 
     def forward(self, inp):
@@ -245,6 +316,8 @@ class DistributedAttentionLayer(DistributedModule):
         else:
             hidden, attention_mask = inp
             cross_states = None
+        if self.memory_layout:
+            return self._forward_memory(hidden, cross_states, attention_mask)
         b, S, H = hidden.shape
         g = _group()
         t = tp_size()
@@ -274,6 +347,53 @@ class DistributedAttentionLayer(DistributedModule):
         if self.layernorm is not None:
             out = self.layernorm(out)
         out = out.reshape(b, S, H)
+        if self.cross_attention:
+            return out, cross_states, attention_mask
+        return out, attention_mask
+
+
+    def _forward_memory(self, hidden, cross_states, attention_mask):
+        """hidden [B, S, H/t] (full batch, hidden-sharded) -> same layout.  q / k / v: partial products over this
+        rank's input features, reduce-scattered over the output features so that each rank ends up with its own
+        heads; the output projection reduce-scatters back to H/t."""
+        from .utils import reduce_scatter_for_tp
+
+        B, S, Hl = hidden.shape
+        g = _group()
+        la, hl, d = self.local_attention_size, self.local_attention_heads, self.attention_head_size
+        A = self.num_attention_heads * d
+        x2 = hidden.reshape(B * S, Hl)
+        h = self.pre_layernorm_mod(x2) if self.pre_layernorm_mod is not None else x2
+        if h.dtype != self.qkv_weight.dtype:
+            h = h.to(self.qkv_weight.dtype)
+        mask = _full_mask(attention_mask, B, g)
+        sizes = self.all_local_attention_sizes
+        if cross_states is None:
+            part = _plain_linear(h, self.qkv_weight).reshape(B * S, 3, A)
+            qkv = reduce_scatter_for_tp(part, 2, split_shapes=sizes)                 # [T, 3, la]
+            if self.qkv_bias is not None:
+                qkv = qkv + self.qkv_bias.reshape(3, la)
+            ctx2 = self.attention_core(qkv.reshape(B * S, 3 * la), B, S, mask)
+        else:
+            Sc = cross_states.shape[1]
+            c2 = cross_states.reshape(-1, Hl).to(self.qkv_weight.dtype)
+            q2 = reduce_scatter_for_tp(_plain_linear(h, self.qkv_weight[:A]), 1, split_shapes=sizes)
+            kv = reduce_scatter_for_tp(_plain_linear(c2, self.qkv_weight[A:]).reshape(-1, 2, A), 2, split_shapes=sizes)
+            if self.qkv_bias is not None:
+                q2 = q2 + self.qkv_bias[:la]
+                kv = kv + self.qkv_bias[la:].reshape(2, la)
+            q = A_ops.tokens_to_heads(q2.reshape(B, S, la), hl)
+            k = A_ops.tokens_to_heads(kv[:, 0].reshape(B, Sc, la), hl)
+            v = A_ops.tokens_to_heads(kv[:, 1].reshape(B, Sc, la), hl)
+            ctx2 = self._attend(q, k, v, B, S, False, mask)
+        out = reduce_scatter_for_tp(_plain_linear(ctx2, self.dense_weight), 1, split_shapes=self.hidden_split)
+        if self.dense_bias is not None:
+            out = out + self.dense_bias
+        out = F.dropout(out, self.hidden_dropout_prob, self.training)
+        out = out.to(x2.dtype) + x2
+        if self.layernorm is not None:
+            out = self.layernorm(out)
+        out = out.reshape(B, S, Hl)
         if self.cross_attention:
             return out, cross_states, attention_mask
         return out, attention_mask
@@ -328,21 +448,40 @@ class DistributedTransformerOutputLayer(DistributedModule):
         self.local_intermediate_size = li = get_local_channels(I)
         self.all_local_intermediate_sizes = [get_local_channels(I, r) for r in range(tp_size())]
         dtype = _param_dtype()
-        with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):
-            with initialize_with_output_partition(self):
-                self.dense1_weight = nn.Parameter(torch.empty(li, H))
-                self.dense1_bias = nn.Parameter(torch.zeros(li))
-            with initialize_with_input_partition(self, exclude_from_dist=["dense2_bias"]):
-                self.dense2_weight = nn.Parameter(torch.empty(H, li))
-                self.dense2_bias = nn.Parameter(torch.zeros(H)) if tp_rank() == 0 else None
-            self._init_weights()
-        with parameter_creation_scope(self, scaled_batch=False, dtype=dtype):
-            mixed = bool(self.fp32_residual_addition)
-            self.pre_layernorm_mod = FusedLayerNorm(H, self.layernorm_epsilon, mixed_dtype=mixed) \
-                if self.pre_layernorm else None
-            self.layernorm = FusedLayerNorm(H, self.layernorm_epsilon) if self.post_layernorm else None
-        self.weight_split_shapes = {"dense1_weight": self.all_local_intermediate_sizes,
-                                    "dense2_weight": self.all_local_intermediate_sizes}
+        self.memory_layout = _memory_layout()
+        self.hidden_split = [get_local_channels(H, r) for r in range(tp_size())]
+        if self.memory_layout:
+            Hl = get_local_channels(H)
+            with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):
+                with initialize_with_input_partition(self):
+                    self.dense1_weight = nn.Parameter(torch.empty(I, Hl))        # every output feature, H/t inputs
+                    self.dense2_weight = nn.Parameter(torch.empty(H, li))
+                with initialize_with_output_partition(self):
+                    self.dense1_bias = nn.Parameter(torch.zeros(li))
+                    self.dense2_bias = nn.Parameter(torch.zeros(Hl))
+                self._init_weights()
+            from .layer_norm import DistributedLayerNorm
+            with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):
+                self.pre_layernorm_mod = DistributedLayerNorm(H, self.layernorm_epsilon) if self.pre_layernorm else None
+                self.layernorm = DistributedLayerNorm(H, self.layernorm_epsilon) if self.post_layernorm else None
+            self.weight_split_shapes = {"dense1_weight": self.hidden_split,
+                                        "dense2_weight": self.all_local_intermediate_sizes}
+        else:
+            with parameter_creation_scope(self, scaled_batch=True, dtype=dtype):
+                with initialize_with_output_partition(self):
+                    self.dense1_weight = nn.Parameter(torch.empty(li, H))
+                    self.dense1_bias = nn.Parameter(torch.zeros(li))
+                with initialize_with_input_partition(self, exclude_from_dist=["dense2_bias"]):
+                    self.dense2_weight = nn.Parameter(torch.empty(H, li))
+                    self.dense2_bias = nn.Parameter(torch.zeros(H)) if tp_rank() == 0 else None
+                self._init_weights()
+            with parameter_creation_scope(self, scaled_batch=False, dtype=dtype):
+                mixed = bool(self.fp32_residual_addition)
+                self.pre_layernorm_mod = FusedLayerNorm(H, self.layernorm_epsilon, mixed_dtype=mixed) \
+                    if self.pre_layernorm else None
+                self.layernorm = FusedLayerNorm(H, self.layernorm_epsilon) if self.post_layernorm else None
+            self.weight_split_shapes = {"dense1_weight": self.all_local_intermediate_sizes,
+                                        "dense2_weight": self.all_local_intermediate_sizes}
         ren = {"dense1_weight": "dense1.weight", "dense1_bias": "dense1.bias", "dense2_weight": "dense2.weight",
                "dense2_bias": "dense2.bias", "pre_layernorm_mod.weight": "pre_layernorm.weight",
                "pre_layernorm_mod.bias": "pre_layernorm.bias"}
@@ -378,6 +517,11 @@ class DistributedTransformerOutputLayer(DistributedModule):
 
     def state_dict_layout(self):
         sz = self.all_local_intermediate_sizes
+        if self.memory_layout:
+            hs = self.hidden_split
+            return {"dense1.weight": (1, hs), "dense1.bias": (0, sz), "dense2.weight": (1, sz), "dense2.bias": (0, hs),
+                    "pre_layernorm.weight": (0, hs), "pre_layernorm.bias": (0, hs), "layernorm.weight": (0, hs),
+                    "layernorm.bias": (0, hs)}
         return {"dense1.weight": (0, sz), "dense1.bias": (0, sz), "dense2.weight": (1, sz),
                 "dense2.bias": ("one_rank", None)}
 
@@ -394,7 +538,30 @@ class DistributedTransformerOutputLayer(DistributedModule):
             return F.gelu(h, approximate="tanh")
         return getattr(F, self.activation)(h)
 
+    def _forward_memory(self, hidden):
+        """[B, S, H/t] -> [B, S, H/t]: both projections produce partial sums over this rank's input features and are
+        reduce-scattered over their output features."""
+        from .utils import reduce_scatter_for_tp
+
+        shape = hidden.shape
+        x2 = hidden.reshape(-1, shape[-1])
+        h = self.pre_layernorm_mod(x2) if self.pre_layernorm_mod is not None else x2
+        if h.dtype != self.dense1_weight.dtype:
+            h = h.to(self.dense1_weight.dtype)
+        inter = reduce_scatter_for_tp(_plain_linear(h, self.dense1_weight), 1,
+                                      split_shapes=self.all_local_intermediate_sizes) + self.dense1_bias
+        inter = self._act_other(inter)
+        out = reduce_scatter_for_tp(_plain_linear(inter, self.dense2_weight), 1, split_shapes=self.hidden_split)
+        out = out + self.dense2_bias
+        out = F.dropout(out, self.hidden_dropout_prob, self.training)
+        out = out.to(x2.dtype) + x2
+        if self.layernorm is not None:
+            out = self.layernorm(out)
+        return out.reshape(shape)
+
     def forward(self, hidden):
+        if self.memory_layout:
+            return self._forward_memory(hidden)
         shape = hidden.shape
         H = shape[-1]
         g = _group()
@@ -437,6 +604,11 @@ class DistributedTransformerLayer(DistributedModule):
         cfg = parse_args(args, kwargs, self._KEYS, self)
         if self.parallel_attn_output and self.add_cross_attention:
             raise DistTransformerConfigError("parallel_attn_output is not supported with cross attention")
+        self.memory_layout = _memory_layout()
+        self.hidden_split = [get_local_channels(self.hidden_size, r) for r in range(tp_size())]
+        if self.memory_layout and self.parallel_attn_output:
+            raise DistTransformerConfigError("optimize='memory' does not support parallel_attn_output (GPT-J / "
+                                             "GPT-NeoX style blocks); use optimize='speed'")
         # GPT-J: one LayerNorm feeds both branches (single_pre_layernorm); GPT-NeoX: each branch has its own
         attn_cfg = update_copy_dict(cfg, cross_attention=False)
         out_cfg = dict(cfg)
@@ -454,7 +626,21 @@ class DistributedTransformerLayer(DistributedModule):
         else:
             hidden, attention_mask = inp[0], inp[1]
             cross_states = cross_mask = None
-        if self.parallel_attn_output:
+        if self.memory_layout:
+            from .utils import scatter_and_merge_for_tp
+            if self.input_layer:      # [local batch, S, H] -> [full batch, S, H/t]  (all-to-all, reference :1429-1434)
+                hidden = scatter_and_merge_for_tp(hidden, split_dim=2, merge_dim=0, split_shapes=self.hidden_split)
+            sharded_cross = cross_states
+            if cross_states is not None and (self.input_layer or cross_states.shape[-1] == self.hidden_size):
+                sharded_cross = scatter_and_merge_for_tp(cross_states, split_dim=2, merge_dim=0,
+                                                         split_shapes=self.hidden_split)
+            hidden, _ = self.attention((hidden, attention_mask))
+            if self.cross_attention is not None:
+                hidden, _, _ = self.cross_attention((hidden, sharded_cross, cross_mask))
+            hidden = self.output(hidden)
+            if self.output_layer:     # back to [local batch, S, H]
+                hidden = scatter_and_merge_for_tp(hidden, split_dim=0, merge_dim=2, merge_shapes=self.hidden_split)
+        elif self.parallel_attn_output:
             hidden = self._parallel_forward(hidden, attention_mask)
         else:
             hidden, _ = self.attention((hidden, attention_mask))

@@ -200,7 +200,7 @@ def _allgather_impl(x: torch.Tensor, dim: int, split_shapes=None, group=None) ->
             _throttled(dist.all_gather_into_tensor, out, x, group=group)
             return out
         parts = torch.empty((n,) + tuple(x.shape), dtype=x.dtype, device=x.device)
-        _throttled(dist.all_gather_into_tensor, parts, x, group=group)
+        _throttled(dist.all_gather_into_tensor, parts.view((n * x.shape[0],) + tuple(x.shape[1:])), x, group=group)
         return torch.cat(list(parts.unbind(0)), dim=dim)
     # uneven: pad to the largest shard, gather, trim
     mx = max(split_shapes)
@@ -209,7 +209,7 @@ def _allgather_impl(x: torch.Tensor, dim: int, split_shapes=None, group=None) ->
     padded = x.new_zeros(pad_shape)
     padded.narrow(dim, 0, x.shape[dim]).copy_(x)
     parts = torch.empty((n,) + tuple(pad_shape), dtype=x.dtype, device=x.device)
-    _throttled(dist.all_gather_into_tensor, parts, padded, group=group)
+    _throttled(dist.all_gather_into_tensor, parts.view((n * pad_shape[0],) + tuple(pad_shape[1:])), padded, group=group)
     return torch.cat([parts[r].narrow(dim, 0, split_shapes[r]) for r in range(n)], dim=dim)
 
 
@@ -242,8 +242,8 @@ def _reduce_scatter_impl(x: torch.Tensor, dim: int, split_shapes=None, group=Non
             q.narrow(dim, 0, shapes[k]).copy_(p)
             p = q
         pieces.append(p.contiguous())
-    stacked = torch.stack(pieces, 0)
-    out = torch.empty_like(stacked[0])
+    stacked = torch.cat(pieces, 0)            # rank k's block is rows [k*rows, (k+1)*rows)
+    out = torch.empty_like(pieces[0])
     _throttled(dist.reduce_scatter_tensor, out, stacked, group=group)
     return out.narrow(dim, 0, shapes[r]).contiguous() if shapes[r] != mx else out
 

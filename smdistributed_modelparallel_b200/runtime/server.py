@@ -351,8 +351,10 @@ class _Scheduler:
     test/torch/mpi_4ps/test_deterministic.py:17-122), and the host runs ahead of the GPUs: the order in which
     work is *enqueued* is a 1F1B-style interleave, and the streams + NCCL p2p dependencies pipeline it."""
 
-    def __init__(self, server, jobs, window, warm=None):
-        self.server, self.jobs, self.window = server, list(jobs), window
+    def __init__(self, server, next_job, window, warm=None):
+        # ``next_job()`` -> (microbatch, phase) to start now, or None when nothing can start yet (the policy object
+        # state.pipeline decides: runtime/pipeline.py, reference torch/pipeline.py:9-145).
+        self.server, self.next_job, self.window = server, next_job, window
         # ``warm``: microbatches started back to back before the first resume; after that a new microbatch is
         # started only right after a resume (1F1B-style alternation).  Filling the whole window first would
         # park the first microbatch's loss / backward request behind every later forward on the stream and
@@ -370,20 +372,22 @@ class _Scheduler:
     def run(self):
         srv = self.server
         waiting = []                      # suspended tasks, oldest first
-        nxt = 0
         resumed_since_start = 0
-        while nxt < len(self.jobs) or waiting:
-            can_start = nxt < len(self.jobs) and len(waiting) < self.window
-            if can_start and (len(waiting) < self.warm or resumed_since_start >= 1 or not waiting):
-                task = _Task(self, *self.jobs[nxt])
-                nxt += 1
+        while True:
+            job = None
+            if len(waiting) < self.window and (len(waiting) < self.warm or resumed_since_start >= 1 or not waiting):
+                job = self.next_job()
+            if job is not None:
+                task = _Task(self, *job)
                 resumed_since_start = 0
                 task.thread.start()
-            else:
+            elif waiting:
                 task = waiting.pop(0)
                 resumed_since_start += 1
                 while task.waiting_key not in srv.stash:
                     srv._pump_one(50)
+            else:
+                break
             self._switch_to(task)
             if not task.finished:
                 waiting.append(task)
@@ -930,11 +934,21 @@ class ExecutionServer:
                               "detach": step_fn.detach_outputs}
             try:
                 window = max(1, int(st.cfg.active_microbatches))
-                if st.cfg.pipeline == "interleaved":
-                    _Scheduler(self, [(mb, "both") for mb in range(num_mb)], window, warm=self.core.pp_size()).run()
-                else:           # simple: every forward, then every backward; _only_forward: forwards only
-                    _Scheduler(self, [(mb, "fwd") for mb in range(num_mb)], window).run()
-                    _Scheduler(self, [(mb, "bwd") for mb in range(num_mb) if mb in self.deferred_bwd], window).run()
+                interleaved = st.cfg.pipeline == "interleaved"
+
+                def next_job():
+                    # the pipeline policy names the microbatch: ``interleaved`` - one ready for backward before a
+                    # new forward (a microbatch started here runs its backward in the same task, as soon as its
+                    # forward has returned); ``simple`` - every forward, and backwards only once no forward is in
+                    # flight; ``_only_forward`` - forwards only
+                    mb = pipe.get_next_microbatch()
+                    if mb is None:
+                        return None
+                    if pipe.get_status(mb) is MbStatus.READY_FOR_FWD:
+                        return (mb, "both" if interleaved else "fwd")
+                    return (mb, "bwd")
+
+                _Scheduler(self, next_job, window, warm=self.core.pp_size() if interleaved else None).run()
                 outputs = self._step_ctx["outputs"]
             except BaseException as exc:
                 # the other stages are waiting for this step to end: tell them it ended badly, so that the

@@ -154,3 +154,33 @@ def test_checkpointed_hf_blocks_ignore_the_kv_cache():
     ref = dict(oracle.named_parameters())
     worst = max((p.grad - ref[n].grad).abs().max().item() for n, p in net.named_parameters())
     assert abs(loss - ol.item()) < 1e-6 and worst < 1e-6, (loss, ol.item(), worst)
+
+
+def test_checkpoint_attentions_wraps_the_library_attention_path(monkeypatch):
+    """``checkpoint_attentions`` (reference torch/nn/transformer.py:1487-1493): where attention runs as separate
+    library ops (CPU here; additive position bias on the GPU) the core is recomputed in backward instead of keeping the
+    [B, heads, Sq, Sk] probabilities; gradients are unchanged."""
+    import torch.utils.checkpoint as tuc
+
+    import smdistributed_modelparallel_b200 as smp
+
+    kw = dict(num_attention_heads=2, attention_head_size=8, hidden_size=16, intermediate_size=32,
+              attention_dropout_prob=0.0, hidden_dropout_prob=0.0, pre_layernorm=True, post_layernorm=False,
+              causal_mask_size=8, use_normal_initialization=True)
+    x0 = torch.randn(2, 8, 16)
+    calls = []
+    real = tuc.checkpoint
+    monkeypatch.setattr(tuc, "checkpoint", lambda fn, *a, **k: (calls.append(1), real(fn, *a, **k))[1])
+    grads = []
+    for flag in (False, True):
+        smp.reset()
+        smp.init({"microbatches": 1, "checkpoint_attentions": flag})
+        torch.manual_seed(0)
+        layer = smp.nn.DistributedTransformerLayer(**kw)
+        x = x0.clone().requires_grad_(True)
+        layer((x, None))[0].square().sum().backward()
+        grads.append((x.grad.clone(), layer.attention.qkv_weight.grad.clone() if layer.attention.qkv_weight.grad is not None
+                      else layer.attention.qkv_weight.main_grad.clone()))
+        assert len(calls) == (1 if flag else 0)
+    assert torch.allclose(grads[0][0], grads[1][0], atol=1e-6)
+    assert torch.allclose(grads[0][1], grads[1][1], atol=1e-6)

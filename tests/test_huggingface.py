@@ -215,3 +215,33 @@ def test_t5_block_hooks_and_additive_position_bias():
     hidden2[1, -1] += 10.0                     # a masked key position of sample 1 ...
     out_c, _ = layer((hidden2, bias + mask))
     assert torch.allclose(out_c[1, :-2], out_b[1, :-2], atol=1e-5)      # ... cannot influence the visible queries
+
+
+def test_match_weights_copies_the_replaced_modules_values():
+    """``_match_weights`` (internal key, reference torch/tp_registry.py:237-242): the distributed replacement starts from
+    the values of the module it replaces, so no state dict has to be loaded to compare the two."""
+    from transformers import GPT2Config, GPT2LMHeadModel
+
+    smp.reset()
+    smp.init({"microbatches": 1, "_match_weights": True})
+    cfg = GPT2Config(n_layer=2, n_head=4, n_embd=32, n_positions=32, vocab_size=96, resid_pdrop=0, embd_pdrop=0,
+                     attn_pdrop=0)
+    torch.manual_seed(5)
+    with smp.tensor_parallelism(enabled=True):
+        hf = GPT2LMHeadModel(cfg).eval()
+    ids = torch.randint(0, cfg.vocab_size, (2, 16))
+    with torch.no_grad():
+        ref = hf(input_ids=ids, labels=ids)
+    model = smp.DistributedModel(hf)
+    assert type(model.module).__name__ == "DistributedTransformerLMHead"
+    model.eval()
+
+    @smp.step
+    def fwd(model, ids):
+        out = model(input_ids=ids, labels=ids)
+        return out.loss, out.logits
+
+    with torch.no_grad():
+        loss, logits = fwd(model, ids)
+    assert abs(loss.reduce_mean().item() - ref.loss.item()) < 1e-5
+    assert (logits.concat() - ref.logits).abs().max().item() < 1e-5

@@ -112,3 +112,28 @@ def test_untraced_time_estimate_ignores_embedding_tables():
     # memory-weighted (the reference's fallback): the embedding table pushes almost every layer to the other stage
     assign = ModulePartitioner(m, 2, memory_weight=1.0).partition()
     assert sum(1 for l in m.layers if assign[l] == assign[m.emb]) <= 2
+
+
+def test_contiguous_false_interleaves_siblings_for_balance():
+    """Costs 5,5,1,1 over two devices: the best contiguous cut is 5 | 7; interleaving gives 6 | 6."""
+    import torch.nn as nn
+
+    from smdistributed_modelparallel_b200.pipeline.partition import ModulePartitioner
+
+    def build():
+        return nn.Sequential(nn.Linear(50, 100, bias=False), nn.Linear(50, 100, bias=False),
+                             nn.Linear(10, 100, bias=False), nn.Linear(10, 100, bias=False))
+
+    def loads(assign, net):
+        out = [0, 0]
+        for m in net:
+            out[assign[m]] += m.weight.numel()
+        return out
+
+    net = build()
+    a = ModulePartitioner(net, 2, memory_weight=1.0).partition()
+    assert [a[m] for m in net] == [0, 1, 1, 1]
+    assert max(loads(a, net)) == 7000
+    net = build()
+    b = ModulePartitioner(net, 2, memory_weight=1.0, contiguous=False).partition()
+    assert loads(b, net) == [6000, 6000]

@@ -157,7 +157,8 @@ def test_leader_scheduler_order_is_static():
 
     def order(nmb, window, warm):
         srv = FakeServer()
-        S._Scheduler(srv, [(mb, "both") for mb in range(nmb)], window, warm=warm).run()
+        jobs = iter([(mb, "both") for mb in range(nmb)])
+        S._Scheduler(srv, lambda: next(jobs, None), window, warm=warm).run()
         return srv.log
 
     got = order(4, 4, 2)
@@ -169,3 +170,55 @@ def test_leader_scheduler_order_is_static():
     assert one == [(mb, seg) for mb in range(3) for seg in range(3)]
     every = sorted(order(8, 4, 2))
     assert every == [(mb, seg) for mb in range(8) for seg in range(3)]
+
+
+def test_scheduler_takes_its_microbatch_order_from_the_pipeline_policy():
+    """The leader's scheduler asks the policy object (SimplePipeline / InterleavedPipeline) which microbatch to start
+    (reference torch/pipeline.py:96-145 get_next_microbatch): ``simple`` starts no backward while a forward is in
+    flight; ``interleaved`` runs a microbatch's backward before starting the next forward once it is ready."""
+    import torch
+
+    from smdistributed_modelparallel_b200.runtime import server as S
+    from smdistributed_modelparallel_b200.runtime.pipeline import InterleavedPipeline, MbStatus, SimplePipeline
+
+    def drive(pipe, window, phase_of):
+        log = []
+
+        class FakeServer:
+            stash = {}
+            state = type("St", (), {"device": torch.device("cpu")})()
+
+            def _pump_one(self, timeout_ms):
+                raise AssertionError("nothing to wait for")
+
+            def _run_microbatch(self, mb, phase):
+                log.append((mb, phase))
+                pipe.promote_status(mb)
+                if phase == "fwd":
+                    key = ("K", mb)
+                    self.stash[key] = True
+                    S._task_local.task.suspend(key)        # a forward that waits for another stage
+                    self.stash.pop(key)
+                    log.append((mb, "fwd_end"))
+                    pipe.mark_ready_for_backward(mb)
+                else:
+                    pipe.mark_done(mb)
+
+        def next_job():
+            mb = pipe.get_next_microbatch()
+            if mb is None:
+                return None
+            return (mb, phase_of(pipe.get_status(mb)))
+
+        S._Scheduler(FakeServer(), next_job, window).run()
+        return log
+
+    phase = lambda st: "fwd" if st is MbStatus.READY_FOR_FWD else "bwd"
+    simple = drive(SimplePipeline(3, 3), 3, phase)
+    first_bwd = next(i for i, e in enumerate(simple) if e[1] == "bwd")
+    assert [e for e in simple[:first_bwd] if e[1] == "fwd_end"] == [(0, "fwd_end"), (1, "fwd_end"), (2, "fwd_end")]
+    assert [e for e in simple if e[1] == "bwd"] == [(0, "bwd"), (1, "bwd"), (2, "bwd")]
+    inter = drive(InterleavedPipeline(3, 3), 3, phase)
+    # microbatch 0's backward starts as soon as its forward has ended, before microbatch 2's forward ends
+    assert inter.index((0, "bwd")) < inter.index((2, "fwd_end"))
+    assert sorted(e for e in inter if e[1] == "bwd") == [(0, "bwd"), (1, "bwd"), (2, "bwd")]
