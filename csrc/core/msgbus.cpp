@@ -10,7 +10,10 @@
 // bootstrapped from torchrun's rendezvous, with one receiver thread (poll) and one sender thread
 // (so sends never block the training thread), and failure propagation: a rank that shuts down with
 // success=0 tells every peer, which then report smpc_bus_peer_failed() (reference
-// backend/core.py:165-188,227-232).
+// backend/core.py:165-188,227-232).  A peer whose connection ends without a goodbye frame (killed process, lost
+// node) is reported the same way, so nobody waits for ever on a rank that is gone.  The listener binds the
+// interface named at rendezvous, a connection has to present the job's token (exchanged through the process group)
+// and a free rank, frames are size-capped and stamped with the rank of the socket they came from.
 #include <arpa/inet.h>
 #include <netdb.h>
 #include <netinet/in.h>
@@ -81,7 +84,17 @@ struct Bus {
   std::map<uint64_t, uint64_t> tx_pending_by_id;  // txid -> outstanding sends
 
   std::string error;
+  uint64_t token = 0;  // per-job secret every connecting peer has to present
 };
+
+constexpr uint64_t kMaxFrameBytes = 1ull << 36;  // 64 GiB: anything larger is a corrupt or hostile header
+
+struct Hello {
+  uint32_t rank;
+  uint32_t magic;
+  uint64_t token;
+};
+constexpr uint32_t kHelloMagic = 0x534d5042u;  // "SMPB"
 
 Bus* g_bus = nullptr;
 std::mutex g_mu;
@@ -126,6 +139,13 @@ void deliver(Bus* b, const Frame& h, std::vector<char>&& data) {
   b->mb_cv.notify_all();
 }
 
+void mark_failed(Bus* b, int peer) {
+  std::lock_guard<std::mutex> lk(b->mb_mu);
+  int none = -1;
+  b->failed_peer.compare_exchange_strong(none, peer);
+  b->mb_cv.notify_all();
+}
+
 void rx_loop(Bus* b) {
   std::vector<pollfd> pfds;
   std::vector<int> peer_of;
@@ -134,22 +154,38 @@ void rx_loop(Bus* b) {
       pfds.push_back(pollfd{b->fds[p], POLLIN, 0});
       peer_of.push_back(p);
     }
-  std::vector<bool> closed(pfds.size(), false);
+  std::vector<bool> closed(pfds.size(), false), goodbye(pfds.size(), false);
+  // a connection that ends, or sends something that is not a frame, before its peer said goodbye: the peer
+  // is gone - wake every waiter with the failure instead of letting them block for ever
+  auto drop = [&](size_t i) {
+    closed[i] = true;
+    pfds[i].fd = -1;  // poll ignores negative fds
+    if (!goodbye[i] && !b->stop.load()) mark_failed(b, peer_of[i]);
+  };
   while (!b->stop.load()) {
     int rc = ::poll(pfds.data(), pfds.size(), 50);
     if (rc <= 0) continue;
     for (size_t i = 0; i < pfds.size(); ++i) {
       if (closed[i] || !(pfds[i].revents & (POLLIN | POLLHUP | POLLERR))) continue;
       Frame h;
-      if (!read_all(pfds[i].fd, &h, sizeof(h))) {
-        closed[i] = true;
-        pfds[i].fd = -1;  // poll ignores negative fds
+      if (!read_all(pfds[i].fd, &h, sizeof(h)) || h.len > kMaxFrameBytes || h.channel > CH_CONTROL) {
+        drop(i);
         continue;
       }
-      std::vector<char> data(h.len);
+      h.src = (uint32_t)peer_of[i];  // the socket says who is talking, not the frame
+      std::vector<char> data;
+      try {
+        data.resize(h.len);
+      } catch (const std::bad_alloc&) {
+        drop(i);
+        continue;
+      }
       if (h.len > 0 && !read_all(pfds[i].fd, data.data(), h.len)) {
-        closed[i] = true;
-        pfds[i].fd = -1;
+        drop(i);
+        continue;
+      }
+      if (h.channel == CH_CONTROL && h.txid == CTL_GOODBYE) {
+        goodbye[i] = true;
         continue;
       }
       deliver(b, h, std::move(data));
@@ -231,11 +267,12 @@ int connect_to(const std::string& host, int port, int timeout_s) {
 
 }  // namespace
 
-// Step 1: open a listening socket on an ephemeral port (returned), before addresses are exchanged.
-SMPC_API int smpc_bus_listen() {
+// Step 1: open a listening socket on an ephemeral port (returned), before addresses are exchanged.  ``host`` is the
+// numeric IPv4 address of the interface to listen on (the one the rendezvous uses); null / empty / unparsable means
+// every interface.
+SMPC_API int smpc_bus_listen_on(const char* host) {
   std::lock_guard<std::mutex> lk(g_mu);
   if (g_bus) return -1;
-  g_bus = new Bus();
   int fd = ::socket(AF_INET, SOCK_STREAM, 0);
   if (fd < 0) return -1;
   int one = 1;
@@ -243,15 +280,28 @@ SMPC_API int smpc_bus_listen() {
   sockaddr_in addr{};
   addr.sin_family = AF_INET;
   addr.sin_addr.s_addr = htonl(INADDR_ANY);
+  if (host && *host) {
+    in_addr a{};
+    if (inet_pton(AF_INET, host, &a) == 1) addr.sin_addr = a;
+  }
   addr.sin_port = 0;
   if (::bind(fd, (sockaddr*)&addr, sizeof(addr)) != 0 || ::listen(fd, 1024) != 0) {
     ::close(fd);
-    return -1;
+    return -1;  // g_bus stays null: a later attempt starts clean
   }
   socklen_t len = sizeof(addr);
   getsockname(fd, (sockaddr*)&addr, &len);
+  g_bus = new Bus();
   g_bus->listen_fd = fd;
   return ntohs(addr.sin_port);
+}
+SMPC_API int smpc_bus_listen() { return smpc_bus_listen_on(nullptr); }
+
+// The job's token: set after listen and before connect, the same value on every rank.
+SMPC_API int smpc_bus_set_token(unsigned long long token) {
+  if (!g_bus) return -1;
+  g_bus->token = (uint64_t)token;
+  return 0;
 }
 
 // Step 2: build the mesh.  peers = "host:port,host:port,..." indexed by rank.  Rank r connects to
@@ -278,20 +328,36 @@ SMPC_API int smpc_bus_connect(int rank, int size, const char* peers, int timeout
   for (int p = 0; p < rank; ++p) {
     int fd = connect_to(addr[p].first, addr[p].second, timeout_s);
     if (fd < 0) return -3;
-    uint32_t me = (uint32_t)rank;
+    Hello me{(uint32_t)rank, kHelloMagic, b->token};
     if (!write_all(fd, &me, sizeof(me))) return -3;
     b->fds[p] = fd;
   }
-  for (int k = rank + 1; k < size; ++k) {
+  // accept until every higher rank has presented itself; a connection with the wrong token, a rank that is out of
+  // range or already connected, or one that does not complete its hello in time is closed and does not count
+  auto deadline = std::chrono::steady_clock::now() + std::chrono::seconds(timeout_s);
+  int missing = size - rank - 1;
+  while (missing > 0) {
+    auto left = std::chrono::duration_cast<std::chrono::milliseconds>(deadline - std::chrono::steady_clock::now());
+    if (left.count() <= 0) return -4;
     pollfd pf{b->listen_fd, POLLIN, 0};
-    if (::poll(&pf, 1, timeout_s * 1000) <= 0) return -4;
+    if (::poll(&pf, 1, (int)left.count()) <= 0) return -4;
     int fd = ::accept(b->listen_fd, nullptr, nullptr);
-    if (fd < 0) return -4;
+    if (fd < 0) continue;
     int one = 1;
     setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
-    uint32_t who = 0;
-    if (!read_all(fd, &who, sizeof(who)) || (int)who <= rank || (int)who >= size) return -4;
-    b->fds[who] = fd;
+    timeval tv{5, 0};
+    setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
+    Hello who{};
+    bool ok = read_all(fd, &who, sizeof(who)) && who.magic == kHelloMagic && who.token == b->token &&
+              (int)who.rank > rank && (int)who.rank < size && b->fds[who.rank] < 0;
+    if (!ok) {
+      ::close(fd);
+      continue;
+    }
+    timeval none{0, 0};
+    setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &none, sizeof(none));
+    b->fds[who.rank] = fd;
+    --missing;
   }
   b->rx = std::thread(rx_loop, b);
   b->tx = std::thread(tx_loop, b);
@@ -416,9 +482,8 @@ SMPC_API int smpc_bus_shutdown(int success) {
   Bus* b = g_bus;
   if (!b) return 0;
   if (b->rank >= 0) {
-    if (!success)
-      for (int p = 0; p < b->size; ++p)
-        if (p != b->rank) enqueue(b, p, CH_CONTROL, CTL_PEER_FAILED, nullptr);
+    for (int p = 0; p < b->size; ++p)
+      if (p != b->rank) enqueue(b, p, CH_CONTROL, success ? CTL_GOODBYE : CTL_PEER_FAILED, nullptr);
     {
       std::unique_lock<std::mutex> tl(b->tx_mu);
       const uint64_t target = b->tx_enqueued;

@@ -10,7 +10,9 @@ extern "C" {
 
 /* ---- message bus (smp_async_send / bcast / recv / wait / poll / retrieve: backend/collectives.py:233-324;
  *      listener: torch/server_comm.py:162-182) */
-int smpc_bus_listen(void);                                              /* -> ephemeral port */
+int smpc_bus_listen(void);                                              /* -> ephemeral port, every interface */
+int smpc_bus_listen_on(const char* ipv4);                               /* -> ephemeral port on one interface */
+int smpc_bus_set_token(unsigned long long token);                       /* job secret checked at connect */
 int smpc_bus_connect(int rank, int size, const char* peers_csv, int timeout_s);
 int smpc_bus_initialized(void);
 int smpc_bus_rank(void);

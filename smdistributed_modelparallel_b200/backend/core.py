@@ -151,19 +151,29 @@ class ModelParallelCore:
 
         # control-plane bus: full TCP mesh keyed by (peer, transaction id)
         if not self._lib.smpc_bus_initialized():
-            port = self._lib.smpc_bus_listen()
+            # listen on the interface that reaches the rendezvous host only; peers must present the job's token
+            # (drawn by rank 0, handed out through the process group) before their frames are read
+            import secrets
+
+            master = os.environ.get("MASTER_ADDR", "127.0.0.1")
+            my_ip = _my_address(master, _env_int('MASTER_PORT', default=29500))
+            local_only = master in ("127.0.0.1", "localhost", "::1")
+            # (a non-loopback rendezvous whose route could not be determined falls back to every interface)
+            bind_ip = my_ip if (local_only or my_ip != "127.0.0.1") else ""
+            port = self._lib.smpc_bus_listen_on(bind_ip.encode())
             if port <= 0:
                 raise InvalidEnvironmentError("message bus could not open a listening socket")
-            master = os.environ.get("MASTER_ADDR", "127.0.0.1")
-            me = f"{_my_address(master, _env_int('MASTER_PORT', default=29500))}:{port}"
+            me = f"{my_ip}:{port}"
             node_name = socket.gethostname()
             gathered = [None] * size
+            mine = (me, node_name, secrets.randbits(63))
             if size > 1:
-                dist.all_gather_object(gathered, (me, node_name), group=self._host_group)
+                dist.all_gather_object(gathered, mine, group=self._host_group)
             else:
-                gathered = [(me, node_name)]
-            peers = ",".join(a for a, _ in gathered)
-            names = [n for _, n in gathered]
+                gathered = [mine]
+            self._lib.smpc_bus_set_token(int(gathered[0][2]))
+            peers = ",".join(g[0] for g in gathered)
+            names = [g[1] for g in gathered]
             uniq = {n: i for i, n in enumerate(dict.fromkeys(names))}
             self._node_of = [uniq[n] for n in names]
             rc = self._lib.smpc_bus_connect(rank, size, peers.encode(), 120)
@@ -300,6 +310,11 @@ class ModelParallelCore:
         if self._lib is not None and self._lib.smpc_timeline_enabled():
             return self._lib.smpc_timeline_flush()
         return -1
+
+    def pool_record(self, delta_alloc, delta_reserved, ok=True):
+        """Account bytes entering (+) / leaving (-) the receive-side device buffers of the pipeline transport."""
+        if self._lib is not None:
+            self._lib.smpc_pool_record(int(delta_alloc), int(delta_reserved), 1 if ok else 0)
 
     def get_and_reset_memory_stats(self):
         out = (ctypes.c_double * 4)()

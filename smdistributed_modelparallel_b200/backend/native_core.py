@@ -20,6 +20,8 @@ P, I, L = c_void_p, c_int, c_longlong
 
 _SIG = {
     "smpc_bus_listen": ([], I),
+    "smpc_bus_listen_on": ([c_char_p], I),
+    "smpc_bus_set_token": ([ctypes.c_ulonglong], I),
     "smpc_bus_connect": ([I, I, c_char_p, I], I),
     "smpc_bus_initialized": ([], I),
     "smpc_bus_rank": ([], I),

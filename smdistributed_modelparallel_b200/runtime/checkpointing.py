@@ -68,7 +68,8 @@ class CheckpointFunction(torch.autograd.Function):
 
         ctx.fn, ctx.skel, ctx.preserve = fn, skel, preserve_rng_state
         ctx.rng = _rng_snapshot() if preserve_rng_state else None
-        ctx.autocast = torch.is_autocast_enabled()
+        dev_type = next((t.device.type for t in tensors if t.device.type != "cpu"), "cpu")
+        ctx.autocast = (dev_type, torch.is_autocast_enabled(dev_type), torch.get_autocast_dtype(dev_type))
         args, kwargs = _unflatten(skel, list(tensors))
         with torch.no_grad():
             out = fn(*args, **kwargs)
@@ -110,7 +111,9 @@ class CheckpointFunction(torch.autograd.Function):
         if ctx.preserve:
             _rng_restore(ctx.rng)
         try:
-            with torch.enable_grad():
+            dev_type, ac_on, ac_dtype = ctx.autocast
+            # backward runs outside the caller's autocast region: recompute under the mode of the first pass
+            with torch.enable_grad(), torch.autocast(dev_type, dtype=ac_dtype, enabled=ac_on):
                 out = ctx.fn(*args, **kwargs)
         finally:
             if ctx.preserve:

@@ -137,6 +137,7 @@ class PipelineP2P:
         # 44.3k tokens/s): an NCCL receive kernel that waits for its sender spins on the GPU for the whole wait and
         # holds up work of other streams queued behind it on the same hardware connection.  So the side stream is
         # an opt-in (SMP_P2P_SIDE_STREAM=1) for platforms where early posting pays.
+        self._pool_step = [0, 0]            # bytes (allocated, reserved) received into device buffers this step
         self._recv_stream = None
         dev = getattr(state, "device", None)
         if dev is not None and dev.type == "cuda" and os.environ.get("SMP_P2P_SIDE_STREAM", "0") == "1":
@@ -211,7 +212,7 @@ class PipelineP2P:
         with ctx:
             for shape, dtype in metas:
                 wire_dtype = torch.uint8 if dtype == torch.bool else dtype
-                buf = torch.empty(shape, dtype=wire_dtype, device=device)
+                buf = self._pool_alloc(shape, wire_dtype, device)
                 if host:
                     works.append(_HostRecv(self.state.comm, src, self._next_host_tx(src, self.me), buf))
                     self.host_stats["received"] += 1
@@ -220,9 +221,35 @@ class PipelineP2P:
                 out.append(buf)
         return out, works
 
+    def _pool_alloc(self, shape, dtype, device):
+        """A receive buffer, counted in the native core's pool metrics (``smp.get_and_reset_memory_stats`` /
+        ``get_and_reset_alloc_stats``; the reference counts its receiver-side D2D pool, backend/core.py:296-312).
+        Allocated = tensor bytes, reserved = what the caching allocator sets aside for them (512 B granules, 2 MiB
+        blocks above 1 MiB).  The buffers of a step are counted as released when the next step begins: received
+        activations live until their microbatch's backward, so the peak is that of one whole step."""
+        n = 1
+        for d in shape:
+            n *= int(d)
+        n *= torch.empty((), dtype=dtype).element_size()
+        gran = (2 << 20) if n > (1 << 20) else 512
+        reserved = -(-n // gran) * gran
+        try:
+            buf = torch.empty(shape, dtype=dtype, device=device)
+        except RuntimeError:            # out of memory: count the failure, let the caller see the error
+            self.state.core.pool_record(0, reserved, ok=False)
+            self.state.core.pool_record(0, -reserved, ok=True)
+            raise
+        self.state.core.pool_record(n, reserved, ok=True)
+        self._pool_step[0] += n
+        self._pool_step[1] += reserved
+        return buf
+
     # ------------------------------------------------------------------ static mode
     def begin_step(self, key):
         cfg = self.state.cfg
+        if self._pool_step[0] or self._pool_step[1]:
+            self.state.core.pool_record(-self._pool_step[0], -self._pool_step[1], ok=True)
+            self._pool_step = [0, 0]
         # posting ahead needs the order of receptions from each source to repeat exactly.  It does when stages
         # only answer the leader; with fast-mode chains over three or more stages a stage is fed by two sources and
         # the order of its answers depends on timing, so the dynamic protocol stays in charge there.

@@ -21,26 +21,22 @@ class RngManager:
         self._seed = 0
 
     def set_state(self, seed: int):
+        """Derive the side stream from ``seed`` without touching the process-wide generators: ``torch.manual_seed``
+        would also reseed every CUDA generator, i.e. wipe a per-rank seed the user set before ``smp.init`` and make
+        all ranks draw the same dropout masks."""
         self._seed = int(seed)
-        cur_cpu = torch.get_rng_state()
-        torch.manual_seed(self._seed)
-        self._cpu_state = torch.get_rng_state()
-        torch.set_rng_state(cur_cpu)
+        self._cpu_state = torch.Generator().manual_seed(self._seed).get_state()
         self._cuda_state = None  # created lazily on first CUDA use
 
     def _ensure_cuda(self):
         if self._cuda_state is None and torch.cuda.is_available():
-            cur = torch.cuda.get_rng_state()
-            torch.cuda.manual_seed(self._seed)
-            self._cuda_state = torch.cuda.get_rng_state()
-            torch.cuda.set_rng_state(cur)
+            dev = torch.device("cuda", torch.cuda.current_device())
+            self._cuda_state = torch.Generator(device=dev).manual_seed(self._seed).get_state()
 
     @contextmanager
     def consistent_rng_state(self, seed=None):
-        if self._cpu_state is None:
-            self.set_state(self._seed)
-        if seed is not None:
-            self.set_state(seed)
+        if self._cpu_state is None or seed is not None:
+            self.set_state(self._seed if seed is None else seed)
         use_cuda = torch.cuda.is_available()
         if use_cuda:
             self._ensure_cuda()

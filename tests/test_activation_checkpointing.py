@@ -184,3 +184,26 @@ def test_checkpoint_attentions_wraps_the_library_attention_path(monkeypatch):
         assert len(calls) == (1 if flag else 0)
     assert torch.allclose(grads[0][0], grads[1][0], atol=1e-6)
     assert torch.allclose(grads[0][1], grads[1][1], atol=1e-6)
+
+
+def test_recomputation_runs_under_the_autocast_mode_of_the_forward_pass():
+    """backward() is called outside the autocast region; the recomputed forward must still use it, otherwise the
+    recomputed activations (and gradients) are those of another dtype."""
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.reset()
+    smp.init({"microbatches": 1})
+    seen = []
+
+    def fn(x, w):
+        y = x @ w
+        seen.append(y.dtype)
+        return y.float().sum(dim=-1)
+
+    x = torch.randn(4, 8, requires_grad=True)
+    w = torch.randn(8, 8, requires_grad=True)
+    with torch.autocast("cpu", dtype=torch.bfloat16):
+        out = smp.checkpoint(fn, x, w)
+    out.sum().backward()
+    assert seen == [torch.bfloat16, torch.bfloat16], seen
+    assert x.grad is not None and w.grad is not None

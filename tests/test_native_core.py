@@ -208,3 +208,71 @@ def test_link_manager_reuses_slots_by_size():
     assert hm.poll(h2)
     hm.clear_handle(h2)
     assert hm.handles() == []
+
+
+def test_message_bus_handshake_token_source_stamp_and_lost_peer():
+    """Robustness of the control bus, driven through the C ABI with a raw socket playing rank 1: a connection that
+    presents the wrong job token is closed and does not take the rank's slot; frames are attributed to the socket's
+    rank whatever their header claims; an oversized length is treated as a broken peer; and a connection that ends
+    without a goodbye frame wakes blocked receivers with the failing rank (a killed process sends nothing)."""
+    import socket
+    import struct
+    import threading
+
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200.backend import native_core
+
+    smp.reset()
+    lib = native_core.load()
+    lib.smpc_bus_shutdown(1)
+    magic = 0x534D5042
+    try:
+        port = lib.smpc_bus_listen_on(b"127.0.0.1")
+        assert port > 0
+        assert lib.smpc_bus_listen_on(b"127.0.0.1") == -1            # already listening
+        assert lib.smpc_bus_set_token(1234) == 0
+        rc = []
+        t = threading.Thread(target=lambda: rc.append(lib.smpc_bus_connect(0, 2, f"127.0.0.1:{port},127.0.0.1:1".encode(), 30)))
+        t.start()
+        rogue = socket.create_connection(("127.0.0.1", port))
+        rogue.sendall(struct.pack("<IIQ", 1, magic, 999))             # right rank, wrong token
+        rogue.settimeout(10)
+        assert rogue.recv(1) == b""                                   # closed by the listener
+        rogue.close()
+        assert t.is_alive()                                           # still waiting for the real rank 1
+        peer = socket.create_connection(("127.0.0.1", port))
+        peer.sendall(struct.pack("<IIQ", 1, magic, 1234))
+        t.join(30)
+        assert rc == [0]
+        # a frame that claims to come from rank 0 is filed under the rank of its socket
+        peer.sendall(struct.pack("<IIQQ", 0, 0, 77, 3) + b"abc")
+        assert lib.smpc_bus_wait(1, 77, 5000) == 3
+        assert lib.smpc_bus_poll(0, 77) == -1
+        assert lib.smpc_bus_peer_failed() == -1
+        # the peer vanishes without saying goodbye
+        peer.close()
+        assert lib.smpc_bus_wait(1, 78, 10000) == -2
+        assert lib.smpc_bus_peer_failed() == 1
+    finally:
+        lib.smpc_bus_shutdown(1)
+    # a clean goodbye is not a failure; an absurd frame length is
+    for goodbye, expect in ((True, -1), (False, 1)):
+        port = lib.smpc_bus_listen_on(b"127.0.0.1")
+        lib.smpc_bus_set_token(5)
+        rc = []
+        t = threading.Thread(target=lambda: rc.append(lib.smpc_bus_connect(0, 2, f"127.0.0.1:{port},127.0.0.1:1".encode(), 30)))
+        t.start()
+        peer = socket.create_connection(("127.0.0.1", port))
+        peer.sendall(struct.pack("<IIQ", 1, magic, 5))
+        t.join(30)
+        assert rc == [0]
+        if goodbye:
+            peer.sendall(struct.pack("<IIQQ", 1, 2, 2, 0))            # control channel, CTL_GOODBYE
+            peer.close()
+            assert lib.smpc_bus_wait(1, 1, 1500) == -1                # plain timeout
+        else:
+            peer.sendall(struct.pack("<IIQQ", 1, 0, 9, 1 << 60))
+            assert lib.smpc_bus_wait(1, 9, 10000) == -2
+        assert lib.smpc_bus_peer_failed() == expect
+        peer.close()
+        lib.smpc_bus_shutdown(1)

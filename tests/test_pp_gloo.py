@@ -49,7 +49,10 @@ def _worker(rank, world, pipeline, microbatches, trace=False):
     part = smp.state.module_manager.partition_info()
     opt.step()
     tr = smp.state.module_manager.trace
-    return {"loss": loss, "oracle": ol.item(), "worst_grad_err": worst, "n_local": n_local,
+    pool = smp.state.core.get_and_reset_memory_stats()
+    allocs = smp.state.core.get_and_reset_alloc_stats()
+    return {"pool_mb": pool["d2d_peak_allocated_mb"], "pool_reserved_mb": pool["d2d_peak_reserved_mb"],
+            "pool_allocs": allocs["success"], "pool_failures": allocs["failure"], "loss": loss, "oracle": ol.item(), "worst_grad_err": worst, "n_local": n_local,
             "ranks_used": sorted(set(part.values())), "hops": smp.state.module_manager.hops,
             "traced": len(tr.order), "trace_time": sum(tr.times.values()), "trace_bytes": sum(tr.memory.values())}
 
@@ -62,6 +65,11 @@ def test_pp2_matches_dense(pipeline):
         assert r["worst_grad_err"] < 1e-5, r
         assert r["ranks_used"] == [0, 1]
         assert r["n_local"] > 0
+        # every stage received tensors from the other one: the transport's receive buffers show up in the native
+        # core's pool metrics (4 microbatches x [2, 16, hidden] fp32 activations at least)
+        assert r["pool_allocs"] >= 4 and r["pool_failures"] == 0, r
+        assert r["pool_mb"] * 2 ** 20 >= 4 * 2 * 16 * CFG["hidden_size"] * 4, r
+        assert r["pool_reserved_mb"] >= r["pool_mb"]
     assert sum(r["n_local"] for r in res) > 0
 
 

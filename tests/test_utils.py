@@ -78,3 +78,27 @@ def test_graph_ancestors_and_unused_parameters():
     lines = log_backward_graph(y.grad_fn)
     assert lines[0].startswith("AddmmBackward0") and any("(parameter)" in ln for ln in lines)
     assert get_ancestors(torch.zeros(2)) == (set(), set())
+
+
+def test_rng_manager_leaves_the_global_generators_alone():
+    """smp.init seeds the tensor-parallel side stream; the default generators keep the seed the user gave them."""
+    import torch
+
+    from smdistributed_modelparallel_b200.utils.random import RngManager
+
+    torch.manual_seed(4321)
+    want = torch.rand(3)
+    torch.manual_seed(4321)
+    mgr = RngManager()
+    mgr.set_state(99)
+    assert torch.equal(torch.rand(3), want)                     # set_state drew nothing and reseeded nothing
+    torch.manual_seed(4321)
+    with mgr.consistent_rng_state():
+        a = torch.rand(3)
+    assert torch.equal(torch.rand(3), want)                     # the block used its own stream
+    assert torch.equal(a, torch.rand(3, generator=torch.Generator().manual_seed(99)))
+    with mgr.consistent_rng_state():
+        b = torch.rand(3)
+    assert not torch.equal(a, b)                                # the side stream advances between blocks
+    with mgr.consistent_rng_state(seed=99):
+        assert torch.equal(torch.rand(3), a)                    # reseeding restarts it
