@@ -190,9 +190,10 @@ def run_product(args, model_name, parallelism, steps, warmup, micro=0, nmb=0, ch
     use_ckpt = checkpoint if checkpoint >= 0 else (args.checkpoint if args.checkpoint >= 0 else (1 if model_name == "gpt-neox-20b" else 0))
     if use_ckpt:
         smp.set_activation_checkpointing(module.transformer.seq_layers, pack_args_as_tuple=True, strategy="each")
-    # pipeline stages are balanced on measured module times (first-step tracing; the parameters are still on the
-    # meta device then and borrow storage for the traced passes)
-    trace = pp > 1 and os.environ.get("BENCH_TRACE", "1") != "0"
+    # pipeline stages are balanced by the partitioner's time estimate (GEMM weights per tp rank; the configuration
+    # measured on 8 GPUs).  BENCH_TRACE=1 balances them on measured module times instead (first-step tracing; the
+    # parameters are still on the meta device then and borrow storage for the traced passes) - measured on 4 GPUs only.
+    trace = pp > 1 and os.environ.get("BENCH_TRACE", "0") != "0"
     model = smp.DistributedModel(module, trace_execution_times=trace)
     optimizer = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-4, betas=(0.9, 0.95),
                                                            weight_decay=0.1),
@@ -348,7 +349,7 @@ def main():
         k2 = max(3, min(args.steps, int(os.environ.get("BENCH_SECONDARY_STEPS", "8"))))
         # the headline line must print whatever happens to the second configuration: every rank arms a watchdog that
         # ends the process (rank 0 printing the line first) if the secondary run has not finished in time
-        limit = float(os.environ.get("BENCH_SECONDARY_TIMEOUT", "420"))
+        limit = float(os.environ.get("BENCH_SECONDARY_TIMEOUT", "300"))
 
         def give_up():
             if line is not None:
@@ -356,6 +357,8 @@ def main():
                 print(json.dumps(line), flush=True)
             os._exit(0)
 
+        if line is not None:                                     # a copy for the log, should the process be killed
+            print("[bench] headline before the secondary run: " + json.dumps(line), file=sys.stderr, flush=True)
         dog = threading.Timer(limit, give_up)
         dog.daemon = True
         dog.start()

@@ -143,6 +143,31 @@ int smpk_qkv_rotary(void* stream, void* fused, void* q, void* k, void* v, int dt
 int smpk_head_transpose(void* stream, const void* src, void* dst, int dtype, int B, int S, int heads, int d,
                         int to_heads_first);
 
+/* ---- fused attention (replaces the reference's baddbmm -> mask -> softmax -> dropout -> matmul composition,
+ * torch/nn/transformer.py:1617-1657, forward and backward; no Sq x Sk tensor is written to memory)
+ * q, k, v, o, d_o, dq, dk, dv: 16-bit, head size d a multiple of 32 in [32, 256], addressed by element strides
+ * (batch, head, sequence; the head dimension is contiguous), so both [B, H, S, d] and [B, S, H, d] work.
+ * lse [B*H*Sq] fp32: per-row log-sum-exp in the log2 domain (+inf for rows with no visible key), written by the
+ * forward and read by the backward.  delta [B*H*Sq] fp32: scratch the backward fills.  scale multiplies q k^T.
+ * causal: key j visible to query i iff j <= i + (Sk - Sq); window > 0 additionally requires j > i + (Sk - Sq) - window.
+ * mask: optional bytes, non-zero = excluded, addressed by (m_sb, m_sh, m_sq) element strides (0 broadcasts) with
+ * contiguous keys.  p_drop > 0: dropout decided by Philox4x32-10 over (seed, offset, batch*head, query, key / 4) - the
+ * backward regenerates the forward's mask from the same seed / offset. */
+int smpk_attn_fwd(void* stream, int dtype, int B, int H, int Sq, int Sk, int d, const void* q, long long q_sb,
+                  long long q_sh, long long q_ss, const void* k, long long k_sb, long long k_sh, long long k_ss,
+                  const void* v, long long v_sb, long long v_sh, long long v_ss, void* o, long long o_sb,
+                  long long o_sh, long long o_ss, float* lse, float scale, int causal, int window, const void* mask,
+                  long long m_sb, long long m_sh, long long m_sq, float p_drop, unsigned long long seed,
+                  unsigned long long offset);
+int smpk_attn_bwd(void* stream, int dtype, int B, int H, int Sq, int Sk, int d, const void* q, long long q_sb,
+                  long long q_sh, long long q_ss, const void* k, long long k_sb, long long k_sh, long long k_ss,
+                  const void* v, long long v_sb, long long v_sh, long long v_ss, const void* o, long long o_sb,
+                  long long o_sh, long long o_ss, const void* d_o, long long g_sb, long long g_sh, long long g_ss,
+                  const float* lse, float* delta, void* dq, long long dq_sb, long long dq_sh, long long dq_ss, void* dk,
+                  long long dk_sb, long long dk_sh, long long dk_ss, void* dv, long long dv_sb, long long dv_sh,
+                  long long dv_ss, float scale, int causal, int window, const void* mask, long long m_sb,
+                  long long m_sh, long long m_sq, float p_drop, unsigned long long seed, unsigned long long offset);
+
 /* ---- multi-tensor apply (amp_C: torch/fp16/fp16.py:132,159,555; torch/apex/optimizers/*.py)
  * lists: array of `depth` pointers, each to an array of n device addresses; sizes: n element counts;
  * dtypes: one code per list; chunk: elements per thread block. noop (device int, optional): skip

@@ -138,6 +138,8 @@ def load_into_model(model, state_dict, strict=True, translate_function=None):
     opt = state.optimizer
     if opt is not None and getattr(opt, "fp16_optimizer", None) is not None:
         opt.fp16_optimizer.copy_model_to_master()
+    if opt is not None and getattr(opt, "_opt_shard", None) is not None:
+        opt._opt_shard.refresh_masters()
     if missing or unexpected:
         get_logger().debug(f"load_state_dict: {len(missing)} missing, {len(unexpected)} unexpected keys")
     return res

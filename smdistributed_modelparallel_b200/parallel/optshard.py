@@ -201,6 +201,13 @@ class OptimizerStateSharding:
                 a, b = sl["seg"]
                 dist.all_gather_into_tensor(self.param_buffer[a:b], self.param_buffer[sl["start"]:sl["end"]], group=group)
 
+    def refresh_masters(self):
+        """The model's parameters were overwritten from outside (``model.load_state_dict`` after the optimizer was
+        built): take the fp32 master slices from them again, as ``copy_model_to_master`` does for per-parameter
+        masters - otherwise the next step would update, and all-gather, the values from before the load."""
+        for sl in self.slices:
+            sl["master"].data.copy_(self.param_buffer[sl["start"]:sl["end"]])
+
     # ------------------------------------------------------------------ checkpointing
     def virtual_named_parameters(self):
         """(name, fp32 master slice) for every slice of the flat buffer this rank owns - the tensors the inner

@@ -710,3 +710,61 @@ def test_reinitialising_with_other_degrees_in_one_process():
         assert [x[:3] for x in r] == [(1, 2, 4), (2, 1, 2), (2, 2, 2)]
         assert all(second < first for *_, first, second in r)
     assert res[0][0][3] == res[0][2][3]            # the same tensor-parallel model whether or not it is pipelined
+
+
+def _tuned_worker(rank, world, record_steps):
+    import os
+
+    import smdistributed_modelparallel_b200 as smp
+
+    os.environ["SMP_SCHEDULE_RECORD_STEPS"] = str(record_steps)
+    smp.init({"pipeline_parallel_degree": 2, "tensor_parallel_degree": 2, "microbatches": 4, "ddp": True,
+              "active_microbatches": 4, "ddp_dist_backend": "gloo"})
+    torch.manual_seed(7)
+    with smp.tensor_parallelism(enabled=True):
+        module = smp.nn.DistributedTransformerLMHead(**CFG)
+    model = smp.DistributedModel(module)
+    opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    torch.manual_seed(11)
+    all_ids = torch.randint(0, CFG["vocab_size"], (7, 16, 16))
+    losses, warms = [], []
+    for it in range(7):
+        ids = all_ids[it, smp.tp_rank() * 8:(smp.tp_rank() + 1) * 8]
+        opt.zero_grad()
+        out = train_step(model, ids)
+        opt.step()
+        losses.append(out.reduce_mean().item())
+        tuners = list(smp.state.exec_server._tuners.values())
+        warms.append(tuners[0].choice if tuners else None)
+    t = tuners[0] if tuners else None
+    return {"losses": losses, "warms": warms, "pp_rank": smp.pp_rank(),
+            "timed": {c: len(v) for c, v in t.times.items()} if t else None,
+            "cands": t.candidates if t else None}
+
+
+def test_schedule_record_and_pick_fastest():
+    """SMP_SCHEDULE_RECORD_STEPS=4 on pp2 x tp2: steps 1-4 are timed under the candidate warm-up depths, at step 5
+    rank 0's fastest candidate becomes the schedule of both leaders, and the numbers are those of an untuned run
+    (the schedule changes the order of work, not the work)."""
+    tuned = run_distributed(_tuned_worker, 4, 4, timeout=420)
+    plain = run_distributed(_tuned_worker, 4, 0, timeout=420)
+    leaders = [r for r in tuned if r["pp_rank"] == 0]
+    assert len(leaders) == 2
+    for r in leaders:
+        assert r["cands"] == [2, 3, 1, 4]
+        assert r["warms"][:5] == [None] * 5 and r["warms"][5] in r["cands"]      # decided when step 5 starts
+        assert r["warms"][5] == r["warms"][6] == leaders[0]["warms"][5]           # the same on every leader
+        assert r["timed"] == {2: 1, 3: 1, 1: 1, 4: 1}                             # step 0 untimed, one step each
+    for r in tuned:
+        if r["pp_rank"] != 0:
+            assert r["cands"] is None                                             # only leaders schedule
+    for a, b in zip(tuned, plain):
+        assert a["losses"] == pytest.approx(b["losses"], abs=1e-6)
+    assert all(r["cands"] is None for r in plain)

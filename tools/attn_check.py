@@ -11,6 +11,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from smdistributed_modelparallel_b200.ops import _native as N  # noqa: E402
+from tools._clocks import clocks  # noqa: E402
 
 
 def ref_attention(q, k, v, scale, causal, window, mask):
@@ -173,12 +174,14 @@ def time_bwd(dev):
             run_bwd(q, k, v, o, do, lse, scale, True)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(10):
-            run_bwd(q, k, v, o, do, lse, scale, True)
-        e1.record()
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / 10
+        iters = 400                       # ~0.4 s per shape: long enough for the clock sampler to see the load
+        with clocks(f"bwd {name}"):
+            e0.record()
+            for _ in range(iters):
+                run_bwd(q, k, v, o, do, lse, scale, True)
+            e1.record()
+            torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
         flops = 10.0 * B * H * S * S * d / 2
         print(f"time bwd {name} B{B} H{H} S{S} d{d} causal: {ms:.3f} ms  {flops / ms / 1e9:.0f} TFLOP/s (5 ideal causal products)", flush=True)
 
@@ -244,12 +247,14 @@ def main():
                 run_fwd(q, k, v, scale, True)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(10):
-                run_fwd(q, k, v, scale, True)
-            e1.record()
-            torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / 10
+            iters = 1500                  # ~0.3-0.8 s per shape (operands of the large shapes exceed the 126 MB L2)
+            with clocks(f"fwd {name}"):
+                e0.record()
+                for _ in range(iters):
+                    run_fwd(q, k, v, scale, True)
+                e1.record()
+                torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / iters
             flops = 4.0 * B * H * S * S * d / 2
             print(f"time fwd {name} B{B} H{H} S{S} d{d} causal: {ms:.3f} ms  {flops / ms / 1e9:.0f} TFLOP/s (causal flops)", flush=True)
     if args.bwd:
