@@ -249,10 +249,12 @@ def run_product(args, model_name, parallelism, steps, warmup, micro=0, nmb=0, ch
     t0 = time.perf_counter()
     e0.record()
     last = None
+    seen = []
     for i in range(steps):
         ids = host_ids[i % len(host_ids)].to(dev, non_blocking=True)
         out = one_step(ids)
         last = float(out.reduce_mean().item())
+        seen.append(round(last, 4))
     e1.record()
     sync_all()
     ms_b = e0.elapsed_time(e1) / steps
@@ -301,7 +303,7 @@ def run_product(args, model_name, parallelism, steps, warmup, micro=0, nmb=0, ch
             "model_tflops_note": "6 x matmul params + full (non-causal) attention products per token; the kernels skip the masked half of causal attention",
             "clocks": clocks,
             "e2e": {"value": round(e2e, 1), "unit": "tokens/s", "h2d_bytes_per_step": per_rank_batch * seq * 8,
-                    "d2h_bytes_per_step": 4 * nmb, "ms_per_step": round(ms_b, 2), "last_loss": last},
+                    "d2h_bytes_per_step": 4 * nmb, "ms_per_step": round(ms_b, 2), "last_loss": last, "losses": seen[-8:]},
             "gpu_launches": launches,
             "peak_mem_gb": round(peak, 1),
         }
