@@ -1,12 +1,15 @@
 """In-tree native build for the B200 libraries.
 
-Two shared objects are produced next to this package (``smdistributed_modelparallel_b200/lib``):
+Three shared objects are produced next to this package (``smdistributed_modelparallel_b200/lib``):
 
 * ``libsmpb200_kernels.so`` - every sm_100a CUDA kernel (``csrc/kernels/sm100/*.cu``), plain C ABI.
 * ``libsmpb200_core.so``    - the host runtime (``csrc/core/*.cpp``, ``csrc/symm/*.cu``): message bus,
   timeline, grad counter, bucket planner, peer-memory handle exchange.
+* ``_smpb200_torch.so``     - the tensor-communication runtime (``csrc/torch_ext/*.cpp``): a PyTorch C++ extension
+  over the c10d process-group API (uneven all-to-all / all-gather, point-to-point handles, the bucket reducer),
+  compiled with the host compiler against this interpreter's torch headers and imported as a Python module.
 
-Both are compiled with ``nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo`` (cross-compiles
+The first two are compiled with ``nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo`` (cross-compiles
 without a GPU) and loaded with ``ctypes`` - the same arrangement as the reference, which loads its
 ``smplib.so`` through ``ctypes.CDLL`` (reference smdistributed/modelparallel/backend/core.py:236).
 The build is incremental: an object is rebuilt only when its source or a header is newer.
@@ -84,17 +87,49 @@ def _build_lib(src_dirs, exts, out: Path, extra, verbose, ptxas_v=False):
     return "\n".join(logs)
 
 
+TORCH_EXT = LIB_DIR / "_smpb200_torch.so"
+CXX = os.environ.get("CXX", "g++")
+
+
+def _build_torch_ext(verbose):
+    """csrc/torch_ext/*.cpp -> lib/_smpb200_torch.so (one translation unit per source, host compiler)."""
+    import sysconfig
+
+    import torch
+    from torch.utils import cpp_extension as ce
+
+    srcs = sorted((ROOT / "csrc" / "torch_ext").glob("*.cpp"))
+    if not srcs:
+        return ""
+    BUILD_DIR.mkdir(parents=True, exist_ok=True)
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    stamp = BUILD_DIR / "_smpb200_torch.torch_version"
+    built_for = stamp.read_text() if stamp.exists() else ""
+    if not _newer(TORCH_EXT, srcs) and built_for == torch.__version__:
+        return ""
+    libdir = ce.library_paths()[0]
+    cmd = [CXX, "-O2", "-std=c++17", "-shared", "-fPIC", "-fvisibility=hidden", "-DTORCH_EXTENSION_NAME=_smpb200_torch",
+           "-DTORCH_API_INCLUDE_EXTENSION_H", f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}"]
+    cmd += [f"-I{i}" for i in ce.include_paths()] + [f"-I{sysconfig.get_paths()['include']}"]
+    cmd += [*srcs, "-o", TORCH_EXT, f"-L{libdir}", "-ltorch", "-ltorch_cpu", "-lc10", "-ltorch_python",
+            f"-Wl,-rpath,{libdir}"]
+    log = _run(cmd, verbose)
+    stamp.write_text(torch.__version__)
+    return log
+
+
 def build(verbose: bool = False, ptxas_v: bool = False) -> dict:
-    """Compile both libraries (incrementally). Returns {"kernels": path, "core": path, "log": str}."""
+    """Compile the libraries (incrementally). Returns {"kernels": path, "core": path, "torch_ext": path, "log": str}."""
     log = []
+    log.append(_build_torch_ext(verbose))
     log.append(_build_lib([ROOT / "csrc" / "kernels" / "sm100"], [".cu"], KERNEL_LIB, [], verbose, ptxas_v) or "")
     log.append(_build_lib([ROOT / "csrc" / "core", ROOT / "csrc" / "symm"], [".cpp", ".cu"], CORE_LIB, [], verbose,
                           ptxas_v) or "")
-    return {"kernels": KERNEL_LIB, "core": CORE_LIB, "log": "\n".join(log)}
+    return {"kernels": KERNEL_LIB, "core": CORE_LIB, "torch_ext": TORCH_EXT, "log": "\n".join(log)}
 
 
 if __name__ == "__main__":
     out = build(verbose="-v" in sys.argv, ptxas_v="--ptxas" in sys.argv)
     if out["log"].strip():
         print(out["log"])
-    print("built:", out["kernels"], out["core"])
+    print("built:", out["kernels"], out["core"], out["torch_ext"])

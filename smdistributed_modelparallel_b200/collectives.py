@@ -10,8 +10,9 @@ collectives.py:214-245, expected results pinned by test/torch/mpi_4ps/test_colle
   (remainder spread over the first ranks), exchange slices all-to-all, concatenate the received slices along
   ``merge_axis``: rank i ends up with the i-th slice of every rank.
 
-Both run on ``torch.distributed`` groups (NCCL on GPUs, gloo on CPU); on one NVSwitch node NCCL's grouped
-send/recv already moves each slice peer-to-peer at link speed, so no separate native path is kept.
+Both run in the native tensor-communication runtime (``csrc/torch_ext/comm_runtime.cpp``: one uneven all-to-all /
+padded all-gather over flat buffers through the c10d process group - NCCL on GPUs, gloo on CPU); ``SMP_NATIVE_COMM=0``
+selects the ``torch.distributed`` formulation below instead.
 """
 
 from __future__ import annotations
@@ -43,6 +44,10 @@ def allgatherv_tensor(tensor: torch.Tensor, counts, group=CommGroup.DP_GROUP) ->
     if flat.numel() != sum(counts):
         raise ValueError(f"allgatherv: buffer holds {flat.numel()} elements, counts sum to {sum(counts)}")
     if n == 1:
+        return tensor
+    from .backend import native_torch
+    if native_torch.enabled() and flat.is_contiguous():
+        native_torch.load().allgatherv(pg, flat, counts)          # csrc/torch_ext/comm_runtime.cpp
         return tensor
     r = dist.get_rank(pg)
     offs = [sum(counts[:i]) for i in range(n)]

@@ -168,6 +168,40 @@ class GradReducer:
     def register_comm_hook(self, state, hook):
         self.comm_hook = (state, hook)
 
+    def _native_reducer(self):
+        """The native bucket reducer over the current gradient buffer (csrc/torch_ext/comm_runtime.cpp
+        ``BucketReducer``: asynchronous launches per slice, uncovered tails, divisor), rebuilt when the buffer is
+        replaced (optimizer-state sharding installs its own).  None when SMP_NATIVE_COMM=0."""
+        from ..backend import native_torch
+
+        gb = self.grad_buffer
+        if gb is None or not native_torch.enabled() or getattr(self, "_native_broken", False):
+            return None
+        key = (id(gb), gb.buffer.data_ptr())
+        if getattr(self, "_native_key", None) != key:
+            try:
+                nt = native_torch.load()
+                red = nt.BucketReducer(gb.buffer, int(self.bucket_elems))
+                ids = {}
+                for region, (ra, rb) in gb.regions.items():
+                    ids[region] = red.add_region(int(ra), int(rb), self._group_of(region))
+            except Exception as e:          # noqa: BLE001 - nothing has been launched yet: the torch.distributed
+                # formulation below does the same work; say so loudly, once
+                from ..backend.logger import get_logger
+                get_logger().error(f"native bucket reducer unavailable ({type(e).__name__}: {e}); reducing gradients "
+                                   "through torch.distributed calls from Python instead")
+                self._native_broken = True
+                return None
+            self._native, self._native_ids, self._native_key = red, ids, key
+            self._native_seen = {"overlapped_elems": 0, "tail_elems": 0}
+        return self._native
+
+    def _pull_native_stats(self):
+        st = dict(self._native.stats())
+        for k in ("overlapped_elems", "tail_elems"):
+            self.stats[k] += st[k] - self._native_seen[k]
+            self._native_seen[k] = st[k]
+
     # ------------------------------------------------------------------ overlap
     def install_overlap(self, root, is_last_microbatch, min_elems=None):
         """Create per-layer buckets under ``root`` and hook their inputs."""
@@ -300,6 +334,12 @@ class GradReducer:
             group = self.rdp_group if is_scaled_batch_parameter(b["params"][0]) else self.dp_group
             if group is None or dist.get_world_size(group) == 1:
                 return
+            from ..backend import native_torch
+            if native_torch.enabled():
+                b["work"] = native_torch.load().FlatBucket(group, [q.grad for q in b["params"]])
+                b["flat"] = None
+                self.stats["overlapped_elems"] += b["work"].numel()
+                return
             b["flat"] = torch.cat([q.grad.reshape(-1) for q in b["params"]])
             b["work"] = dist.all_reduce(b["flat"], group=group, async_op=True)
             self.stats["overlapped_elems"] += b["flat"].numel()
@@ -312,6 +352,11 @@ class GradReducer:
             b["work"].wait()
             if b["dirty"]:                             # reduced too early: redo from the complete .grad at the end
                 b["work"], b["flat"] = None, None
+                continue
+            if b["flat"] is None:                      # native FlatBucket: copies back and divides
+                b["work"].finish(float(scale))
+                done.update(b["params"])
+                b["work"] = None
                 continue
             off = 0
             for q in b["params"]:
@@ -326,6 +371,11 @@ class GradReducer:
 
     def _bucket_ready(self, idx):
         if not self.require_sync or not self.is_last_microbatch() or self.comm_hook is not None or self.joining:
+            return
+        native = self._native_reducer()
+        if native is not None:
+            for region, a, b in self.buckets[idx]["ranges"]:
+                native.launch(self._native_ids[region], int(a), int(b))
             return
         buf = self.grad_buffer.buffer
         for region, a, b in self.buckets[idx]["ranges"]:
@@ -370,6 +420,11 @@ class GradReducer:
                     flat = self.grad_buffer.region(region)
                     if flat.numel():
                         _run_comm_hook(self.comm_hook[0], self.comm_hook[1], flat, self.bucket_elems)
+                return
+            native = self._native_reducer()
+            if native is not None and not self._launched:
+                native.finish(float(scale))          # waits, reduces the uncovered tails, divides
+                self._pull_native_stats()
                 return
             self._finish_overlapped()
             self.grad_buffer.buffer.mul_(scale)

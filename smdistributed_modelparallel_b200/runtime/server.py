@@ -102,6 +102,29 @@ class _HostSent:
         self.comm.wait_transaction(self.tx)
 
 
+class _NativeTransfer:
+    """A send / receive issued through the native runtime's ``P2PEngine`` (csrc/torch_ext/comm_runtime.cpp: the
+    handle API of the reference's tensor transport - send / recv return a handle, poll / wait / clear act on it,
+    reference torch/ops.py:34-117), presented with the two methods the handle manager uses."""
+
+    def __init__(self, engine, handle):
+        self.engine, self.handle, self.done = engine, handle, False
+
+    def _finish(self):
+        self.engine.clear(self.handle)          # releases the engine's reference to the tensor
+        self.done = True
+
+    def is_completed(self):
+        if not self.done and self.engine.poll(self.handle):
+            self._finish()
+        return self.done
+
+    def wait(self):
+        if not self.done:
+            self.engine.wait(self.handle)
+            self._finish()
+
+
 class PipelineP2P:
     """Tensor transport between pipeline ranks: one 2-rank group per ordered (src, dst) pair.
 
@@ -139,6 +162,14 @@ class PipelineP2P:
         # holds up work of other streams queued behind it on the same hardware connection.  So the side stream is
         # an opt-in (SMP_P2P_SIDE_STREAM=1) for platforms where early posting pays.
         self._pool_step = [0, 0]            # bytes (allocated, reserved) received into device buffers this step
+        # transfers go through the native runtime's handle engine on gloo; on NCCL that is an opt-in
+        # (SMP_NATIVE_P2P=1) until it has been timed against the torch.distributed calls on GPUs
+        from ..backend import native_torch
+
+        mode = os.environ.get("SMP_NATIVE_P2P", "auto")
+        on_gloo = dist.is_initialized() and dist.get_backend() == "gloo"
+        self._engine = native_torch.load().P2PEngine() if (
+            native_torch.enabled() and (mode == "1" or (mode == "auto" and on_gloo))) else None
         self._recv_stream = None
         dev = getattr(state, "device", None)
         if dev is not None and dev.type == "cuda" and os.environ.get("SMP_P2P_SIDE_STREAM", "0") == "1":
@@ -173,6 +204,9 @@ class PipelineP2P:
                 work, keep = _HostSent(self.state.comm, tx), None
                 self.host_stats["sent"] += 1
                 self.host_stats["bytes"] += n
+            elif self._engine is not None:
+                work = _NativeTransfer(self._engine, self._engine.send(group, w, dist.get_group_rank(group, dst), 0))
+                keep = None                                  # the engine holds the tensor until the handle is cleared
             else:
                 work, keep = dist.isend(w, dst=dst, group=group), w
             self.handles.register_handle(work, self.handles.SEND, keep, self.links.get_link(n))
@@ -217,6 +251,9 @@ class PipelineP2P:
                 if host:
                     works.append(_HostRecv(self.state.comm, src, self._next_host_tx(src, self.me), buf))
                     self.host_stats["received"] += 1
+                elif self._engine is not None:
+                    works.append(_NativeTransfer(self._engine,
+                                                 self._engine.recv(group, buf, dist.get_group_rank(group, src), 0)))
                 else:
                     works.append(dist.irecv(buf, src=src, group=group))
                 out.append(buf)

@@ -63,7 +63,9 @@ def _dp_worker(rank, world, shard, bf16, hook=None):
         oopt.step()
     worst = max((a.float() - b).abs().max().item() for a, b in zip(model.module.parameters(), oracle.parameters()))
     stats = dict(model.reducer.stats) if model.reducer is not None else {}
-    return {"worst": worst, "losses": losses, "stats": stats, "buckets": len(getattr(model.reducer, "buckets", []))}
+    native = type(getattr(model.reducer, "_native", None)).__name__ if model.reducer is not None else None
+    return {"worst": worst, "losses": losses, "stats": stats, "buckets": len(getattr(model.reducer, "buckets", [])),
+            "native": native}
 
 
 @pytest.mark.parametrize("shard,bf16", [(False, False), (True, False), (True, True), (False, True)])
@@ -78,6 +80,7 @@ def test_dp2_matches_dense(shard, bf16):
         if bf16 and not shard:
             # 16-bit training without optimizer-state sharding: the two layers are reduced while backward runs
             assert r["buckets"] == 2 and r["stats"]["overlapped_elems"] > 0 and r["stats"]["tail_elems"] > 0, r
+            assert r["native"] == "BucketReducer", r["native"]       # csrc/torch_ext/comm_runtime.cpp did the reducing
     assert abs(res[0]["worst"] - res[1]["worst"]) < 1e-6 or bf16
 
 

@@ -1,0 +1,114 @@
+"""The native tensor-communication runtime (csrc/torch_ext/comm_runtime.cpp, a PyTorch C++ extension over c10d) on four
+gloo ranks: uneven split / merge all-to-all and variable-count all-gather against their definitions (the expectations
+of reference test/torch/mpi_4ps/test_collectives.py:13-114), point-to-point transfers through handles (reference
+torch/ops.py:34-117), and the bucket reducer - early launches, uncovered tails, per-region groups, divisor (reference
+torch/ddp_model.py:336-374)."""
+
+import torch
+
+from dist_utils import run_distributed
+
+
+def _worker(rank, world):
+    import torch.distributed as dist
+
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200.backend import native_torch
+
+    smp.init({"tensor_parallel_degree": 2, "ddp": True, "ddp_dist_backend": "gloo"})
+    nt = native_torch.load()
+    pg = smp.get_world_process_group()
+    out = {}
+    # ---- split / merge all-to-all: every rank holds [6 + rank, 7, 3]; dim 1 is split 2,2,2,1; dim 0 merged
+    x = torch.arange((6 + rank) * 7 * 3, dtype=torch.float32).reshape(6 + rank, 7, 3) + 1000 * rank
+    y = nt.scatter_and_merge(pg, x, 1, 0)
+    out["a2a"] = y
+    # explicit shapes, negative dims, merge along the last dim
+    z = nt.scatter_and_merge(pg, x.transpose(0, 2).contiguous(), -2, -1, [1, 3, 2, 1], [6, 7, 8, 9])
+    out["a2a_explicit"] = z
+    # ---- variable-count all-gather
+    counts = [3, 0, 5, 2]
+    flat = torch.full((10,), -1.0)
+    off = sum(counts[:rank])
+    flat[off:off + counts[rank]] = float(rank + 1)
+    nt.allgatherv(pg, flat, counts)
+    out["agv"] = flat
+    even = torch.zeros(8)
+    even[2 * rank:2 * rank + 2] = rank + 1
+    nt.allgatherv(pg, even, [2, 2, 2, 2])
+    out["agv_even"] = even
+    # ---- p2p handles: a ring, tags keep two messages apart
+    eng = nt.P2PEngine()
+    nxt, prv = (rank + 1) % world, (rank - 1) % world
+    a, b = torch.full((5,), float(rank)), torch.full((3, 2), float(rank) + 0.5)
+    ra, rb = torch.empty(5), torch.empty(3, 2)
+    hr1, hr2 = eng.recv(pg, ra, prv, 1), eng.recv(pg, rb, prv, 2)
+    hs1, hs2 = eng.send(pg, a, nxt, 1), eng.send(pg, b, nxt, 2)
+    got_b = eng.get_ready_tensor(hr2)
+    got_a = eng.get_ready_tensor(hr1)
+    eng.wait(hs1)
+    eng.wait(hs2)
+    assert eng.poll(hs1) and eng.poll(hr1)
+    out["p2p"] = (got_a.clone(), got_b.clone(), got_a.data_ptr() == ra.data_ptr())
+    st = eng.stats()
+    out["p2p_stats"] = (st["sent"], st["received"], st["bytes_sent"], st["pending"])
+    assert eng.reap_sends() == 0
+    eng.clear(hr1)
+    eng.clear(hr2)
+    out["p2p_pending_after"] = eng.pending()
+    try:
+        eng.poll(hr1)
+        out["cleared_handle_refused"] = False
+    except RuntimeError:
+        out["cleared_handle_refused"] = True
+    # ---- bucket reducer: region 0 [0, 40) over the tp group (2 ranks), region 1 [40, 100) over the world
+    buf = torch.arange(100, dtype=torch.float32) * (rank + 1)
+    red = nt.BucketReducer(buf, 16)
+    r0 = red.add_region(0, 40, smp.get_tp_process_group())
+    r1 = red.add_region(40, 100, pg)
+    r_none = red.add_region(100, 100, None)
+    assert red.launch(r1, 60, 80) is True
+    assert red.launch(r1, 70, 90) is False          # overlaps a slice already on its way
+    assert red.launch(r0, 0, 8) is True
+    assert red.launch(r_none, 100, 100) is False
+    assert red.in_flight() == 2
+    red.finish(0.5)
+    out["reduced"] = buf.clone()
+    out["red_stats"] = dict(red.stats())
+    # ---- flat bucket of separate gradient tensors
+    g1, g2 = torch.full((2, 3), float(rank)), torch.full((4,), 10.0 * rank)
+    fb = nt.FlatBucket(pg, [g1, g2])
+    fb.finish(0.25)
+    out["flat"] = (g1.clone(), g2.clone(), fb.numel())
+    dist.barrier()
+    return out
+
+
+def test_native_runtime_on_four_ranks():
+    res = run_distributed(_worker, 4, timeout=300)
+    n = 4
+    xs = [torch.arange((6 + r) * 7 * 3, dtype=torch.float32).reshape(6 + r, 7, 3) + 1000 * r for r in range(n)]
+    split = [2, 2, 2, 1]
+    for r, out in enumerate(res):
+        lo = sum(split[:r])
+        want = torch.cat([x[:, lo:lo + split[r]] for x in xs], dim=0)
+        assert torch.equal(out["a2a"], want)
+        xt = [x.transpose(0, 2).contiguous() for x in xs]                 # [3, 7, 6 + k]
+        es = [1, 3, 2, 1]
+        lo = sum(es[:r])
+        want = torch.cat([t[:, lo:lo + es[r]] for t in xt], dim=2)
+        assert torch.equal(out["a2a_explicit"], want)
+        assert out["agv"].tolist() == [1, 1, 1, 3, 3, 3, 3, 3, 4, 4]
+        assert out["agv_even"].tolist() == [1, 1, 2, 2, 3, 3, 4, 4]
+        prv = (r - 1) % n
+        ga, gb, same = out["p2p"]
+        assert torch.equal(ga, torch.full((5,), float(prv))) and torch.equal(gb, torch.full((3, 2), prv + 0.5)) and same
+        assert tuple(out["p2p_stats"]) == (2, 2, 5 * 4 + 6 * 4, 4)
+        assert out["p2p_pending_after"] == 0 and out["cleared_handle_refused"]   # sends reaped, receives cleared
+        base = torch.arange(100, dtype=torch.float32)
+        tp_sum = (1 + 2) if r < 2 else (3 + 4)                            # tp groups are {0, 1} and {2, 3}
+        want = torch.cat([base[:40] * tp_sum, base[40:] * 10]) * 0.5
+        assert torch.equal(out["reduced"], want), (out["reduced"] - want).abs().max()
+        assert out["red_stats"] == {"overlapped_elems": 28, "tail_elems": 32 + 40}
+        g1, g2, numel = out["flat"]
+        assert torch.equal(g1, torch.full((2, 3), 6 * 0.25)) and torch.equal(g2, torch.full((4,), 60 * 0.25)) and numel == 10

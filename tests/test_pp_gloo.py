@@ -51,7 +51,9 @@ def _worker(rank, world, pipeline, microbatches, trace=False):
     tr = smp.state.module_manager.trace
     pool = smp.state.core.get_and_reset_memory_stats()
     allocs = smp.state.core.get_and_reset_alloc_stats()
-    return {"pool_mb": pool["d2d_peak_allocated_mb"], "pool_reserved_mb": pool["d2d_peak_reserved_mb"],
+    eng = smp.state.exec_server.p2p._engine
+    native = dict(eng.stats()) if eng is not None else None
+    return {"native_p2p": native, "pool_mb": pool["d2d_peak_allocated_mb"], "pool_reserved_mb": pool["d2d_peak_reserved_mb"],
             "pool_allocs": allocs["success"], "pool_failures": allocs["failure"], "loss": loss, "oracle": ol.item(), "worst_grad_err": worst, "n_local": n_local,
             "ranks_used": sorted(set(part.values())), "hops": smp.state.module_manager.hops,
             "traced": len(tr.order), "trace_time": sum(tr.times.values()), "trace_bytes": sum(tr.memory.values())}
@@ -70,6 +72,8 @@ def test_pp2_matches_dense(pipeline):
         assert r["pool_allocs"] >= 4 and r["pool_failures"] == 0, r
         assert r["pool_mb"] * 2 ** 20 >= 4 * 2 * 16 * CFG["hidden_size"] * 4, r
         assert r["pool_reserved_mb"] >= r["pool_mb"]
+        # ... and were moved by the native runtime's handle engine (csrc/torch_ext/comm_runtime.cpp)
+        assert r["native_p2p"]["sent"] >= 4 and r["native_p2p"]["received"] >= 4 and r["native_p2p"]["pending"] == 0, r
     assert sum(r["n_local"] for r in res) > 0
 
 
