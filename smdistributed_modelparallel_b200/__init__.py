@@ -69,6 +69,12 @@ def init(config=None):
     from .parallel import tp_ops
 
     tp_ops.set_comm_mode(tp_ops.select_comm_mode(cfg, torch.cuda.is_available()))
+    # the native tensor-communication runtime (gradient reducer, uneven collectives, p2p handles): a missing or
+    # stale library is reported here, at start-up, not at the first collective that needs it
+    from .backend import native_torch
+
+    if native_torch.enabled():
+        native_torch.load()
     if core.rank() == 0:
         cfg.display_config()
 

@@ -164,6 +164,7 @@ class OptimizerStateSharding:
         self._step += 1
         if adam_like:
             adamw = name == "AdamW" or getattr(opt, "adam_w_mode", 0) == 1
+            pending = []
             for sl in self.slices:
                 group = opt.param_groups[sl["gi"]]
                 m = sl["master"]
@@ -182,6 +183,11 @@ class OptimizerStateSharding:
                                      inv, clip)
                 if self.param_dtype == torch.float32:
                     self.param_buffer[sl["start"]:sl["end"]].copy_(m.data)
+                # this slice is final: its all-gather starts now and runs under the update of the next slices
+                self._gather_slice(sl, pending)
+            for w in pending:
+                w.wait()
+            return None
         else:
             factor = inv * (float(clip.item()) if clip is not None else 1.0)
             if factor != 1.0:
@@ -192,6 +198,15 @@ class OptimizerStateSharding:
                 self.param_buffer[sl["start"]:sl["end"]].copy_(sl["master"].data)
         self.all_gather_params()
         return None
+
+    def _gather_slice(self, sl, pending):
+        """Asynchronous in-place all-gather of one updated slice's segment (reference torch/optimizers/optimizer.py:
+        355-391 gathers after the whole update; here the gather of slice i overlaps the Adam kernel of slice i+1)."""
+        group, n, r = self.groups[sl["region"]]
+        if n > 1:
+            a, b = sl["seg"]
+            pending.append(dist.all_gather_into_tensor(self.param_buffer[a:b], self.param_buffer[sl["start"]:sl["end"]],
+                                                       group=group, async_op=True))
 
     def all_gather_params(self):
         """Rebuild the full parameters from the updated slices (in-place all-gather per segment)."""
