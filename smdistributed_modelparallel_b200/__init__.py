@@ -130,6 +130,14 @@ def mp_size(): return core.mp_size()
 def num_microbatches(): return state.num_microbatches()
 
 
+# ---- global ranks of the groups this rank belongs to (reference torch/core.py:30-34)
+def get_dp_group(pp_rank=None): return core.get_dp_group(pp_rank)
+def get_pp_group(dp_rank=None): return core.get_pp_group(dp_rank)
+def get_mp_group(rdp_rank=None): return core.get_mp_group(rdp_rank)
+def get_tp_group(pp_rank=None, rdp_rank=None): return core.get_tp_group(pp_rank, rdp_rank)
+def get_rdp_group(pp_rank=None, tp_rank=None): return core.get_rdp_group(pp_rank, tp_rank)
+
+
 def param_shard_rank():
     """Rank inside the sharded-data-parallel shard group (reference torch/core.py:37-60)."""
     deg = state.cfg.sharded_data_parallel_degree
@@ -177,7 +185,8 @@ __all__ = [
     "set_activation_checkpointing", "checkpoint", "checkpoint_sequential", "model_creation",
     "delay_param_initialization", "tp_register", "tp_register_with_module", "rank", "size", "local_rank",
     "local_size", "dp_rank", "dp_size", "pp_rank", "pp_size", "tp_rank", "tp_size", "rdp_rank", "rdp_size",
-    "mp_rank", "mp_size", "num_microbatches", "param_shard_rank", "param_shard_size", "get_dp_process_group",
+    "mp_rank", "mp_size", "num_microbatches", "param_shard_rank", "param_shard_size", "get_dp_group", "get_pp_group",
+    "get_mp_group", "get_tp_group", "get_rdp_group", "get_dp_process_group",
     "get_mp_process_group", "get_pp_process_group", "get_tp_process_group", "get_rdp_process_group",
     "get_world_process_group", "CommGroup", "RankType", "WORLD", "PP_GROUP", "TP_GROUP", "DP_GROUP", "RDP_GROUP",
     "MP_GROUP", "broadcast", "send", "recv_from", "allgather", "gather", "barrier", "pp_barrier", "tp_barrier",

@@ -655,12 +655,9 @@ class DistributedModel(nn.Module):
         return _do(self)
 
     def load_saved_partition(self, partition_info):
-        mm = state.module_manager
-        for name, part in partition_info.items():
-            try:
-                mm.set_partition(mm.get_module(name), part)
-            except Exception:
-                pass
+        """Use the module -> pipeline-rank assignment of an earlier run (``state.module_manager.
+        get_model_partition_info()``) instead of partitioning again (reference model.py:936-942)."""
+        state.module_manager.load_partition(partition_info)
 
 
 # ---------------------------------------------------------------------------------------- helpers

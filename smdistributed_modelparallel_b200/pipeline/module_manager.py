@@ -199,6 +199,47 @@ class ModuleManager:
     def module_names(self):
         return list(self._by_name)
 
+    # ---- read-only accessors under the reference's names (torch/module_manager.py:330-520)
+    def get_module_names(self):
+        return self.module_names()
+
+    def get_parent_module(self, module):
+        parents = self.get_parent_modules(module)
+        return parents[0] if parents else None
+
+    def is_main_module(self, module) -> bool:
+        return module is getattr(self, "_root", None)
+
+    def get_parameters(self, module, recurse=True):
+        return list(module.parameters(recurse=recurse))
+
+    @staticmethod
+    def is_distributed(tensor) -> bool:
+        from ..nn.utils import is_distributed_parameter
+        return is_distributed_parameter(tensor)
+
+    is_distributed_parameter = is_distributed_buffer = is_distributed
+
+    @staticmethod
+    def is_scaled_batch_parameter(tensor) -> bool:
+        from ..nn.utils import is_scaled_batch_parameter
+        return is_scaled_batch_parameter(tensor)
+
+    is_scaled_batch_buffer = is_scaled_batch_parameter
+
+    @staticmethod
+    def is_one_rank_parameter(tensor) -> bool:
+        from ..nn.utils import is_one_rank_parameter
+        return is_one_rank_parameter(tensor)
+
+    is_one_rank_buffer = is_one_rank_parameter
+
+    @staticmethod
+    def get_parameter_distribution_axis(tensor):
+        return getattr(tensor, "_smp_dist_axis", None)
+
+    get_buffer_distribution_axis = get_parameter_distribution_axis
+
     # ------------------------------------------------------------------ partition map
     def manual_partition_of(self, module):
         return self._module_partition.get(module)
@@ -222,6 +263,37 @@ class ModuleManager:
 
     def partition_info(self) -> dict:
         return dict(self._partition_by_name)
+
+    def get_model_partition_info(self) -> dict:
+        """Module name -> pipeline rank of the partitioned model: what ``load_saved_partition`` takes (reference
+        torch/module_manager.py:1054-1059, test/torch/mpi_4ps/test_load_partition.py)."""
+        return self.partition_info()
+
+    def load_partition(self, partition_info):
+        """Adopt a saved assignment instead of partitioning: it wins over ``auto_partition`` and over
+        ``smp.set_partition`` calls made afterwards; modules the saved assignment does not name follow their
+        closest named ancestor.  Only before the first step."""
+        if self.partitioned:
+            from ..backend.exceptions import StepFunctionCalledError
+            raise StepFunctionCalledError("a saved partition must be loaded before the first step")
+        loaded = {}
+        for name, part in dict(partition_info).items():
+            self._check_partition_id(int(part))
+            loaded[str(name)] = int(part)
+        self._loaded_partition = loaded
+
+    def loaded_partition(self):
+        return getattr(self, "_loaded_partition", None)
+
+    def assignment_from_saved(self, loaded) -> dict:
+        default = self.cfg.default_partition if (self.cfg is not None and self.cfg.default_partition is not None) else 0
+        out = {}
+        for name in self._by_name:
+            probe = name
+            while probe not in loaded and "/" in probe:
+                probe = probe.rsplit("/", 1)[0]
+            out[name] = loaded.get(probe, default)
+        return out
 
     def is_executor(self, module, pp_rank) -> bool:
         return self.get_partition(module) == pp_rank

@@ -663,9 +663,20 @@ class ExecutionServer:
         st = self.state
         mm = st.module_manager
         times = memory = None
-        if step_fn is not None and st.cfg.auto_partition:
-            times, memory = self._trace(step_fn, args, kwargs, num_mb)
-        assignment = partition_model(self.model.module, mm, st.cfg, module_times=times, module_memory=memory)
+        saved = mm.loaded_partition()
+        path = st.cfg.partition_file or "./partition.data"
+        if saved is None and st.cfg.load_partition:
+            # config keys load_partition / partition_file (the reference reads them in its TensorFlow partitioner,
+            # tensorflow/auto.py:181-233; here they do the same job for the module tree)
+            import pickle
+            with open(path, "rb") as f:
+                saved = {str(k): int(v) for k, v in pickle.load(f).items()}
+        if saved is not None:
+            assignment = mm.assignment_from_saved(saved)
+        else:
+            if step_fn is not None and st.cfg.auto_partition:
+                times, memory = self._trace(step_fn, args, kwargs, num_mb)
+            assignment = partition_model(self.model.module, mm, st.cfg, module_times=times, module_memory=memory)
         # one assignment for the whole job: measured times differ from leader to leader, and the tensor-parallel
         # and data-parallel peers of a stage must all cut the model in the same place, so rank 0's copy is
         # authoritative for everyone (the reference also partitions on rank 0 and broadcasts, torch/server.py:254-268)
@@ -682,6 +693,10 @@ class ExecutionServer:
                         break
                     self._early.append((src, tx, obj))      # a stage that already has its copy may be ahead of us
         mm.assign_partitions(assignment)
+        if st.cfg.partition_file and not st.cfg.load_partition and self.me == 0:
+            import pickle
+            with open(st.cfg.partition_file, "wb") as f:
+                pickle.dump(dict(assignment), f)
         self.model.post_partition()
         self._install_dispatchers()
         self.partitioned = True

@@ -176,6 +176,14 @@ class ModelParallelState:
         return v
 
     # ------------------------------------------------------------------ microbatch bookkeeping
+    def current_step_func(self):
+        """Id of the step function being executed (reference torch/state_mod.py: keys of per-step-function records)."""
+        return self.current_step_func_id
+
+    def current_minibatch(self):
+        srv = self.exec_server
+        return getattr(srv, "_step", 0) if srv is not None else 0
+
     def num_microbatches(self) -> int:
         return self.cfg.microbatches
 

@@ -78,3 +78,27 @@ def test_partition_display_and_local_views_under_pp():
     assert res[0]["local"] == ["a.weight", "a.bias"]
     assert res[1]["local"] == ["bn.weight", "bn.bias", "b.weight", "b.bias"]
     assert res[0]["all"] == res[1]["all"] and len(res[0]["all"]) == 6
+
+
+def test_module_manager_accessors_under_the_reference_names():
+    import torch.nn as nn
+
+    import smdistributed_modelparallel_b200 as smp
+
+    smp.reset()
+    smp.init({"microbatches": 1})
+    net = nn.Sequential(nn.Linear(4, 4), nn.Sequential(nn.Linear(4, 4), nn.ReLU()))
+    model = smp.DistributedModel(net)
+    mm = smp.state.module_manager
+    assert mm.get_module_names()[0] == "main" and "main/1/0" in mm.get_module_names()
+    assert mm.is_main_module(model.module) and not mm.is_main_module(net[1])
+    assert mm.get_parent_module(net[1][0]) is net[1] and mm.get_parent_module(model.module) is None
+    assert len(mm.get_parameters(net[1])) == 2 and len(mm.get_parameters(net, recurse=False)) == 0
+    p = net[0].weight
+    assert not mm.is_distributed(p) and not mm.is_scaled_batch_parameter(p) and not mm.is_one_rank_parameter(p)
+    assert mm.get_parameter_distribution_axis(p) is None
+    lin = smp.nn.DistributedLinear(4, 4)
+    assert mm.is_distributed_parameter(lin.weight) and mm.get_parameter_distribution_axis(lin.weight) == 1
+    assert mm.is_scaled_batch_parameter(lin.weight)
+    assert set(mm.get_model_partition_info().values()) == {0} and smp.state.current_minibatch() == 0   # pp = 1: all on rank 0
+    assert smp.get_dp_group() == [0] and smp.get_pp_group() == [0] and smp.get_tp_group() == [0]

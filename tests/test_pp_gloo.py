@@ -772,3 +772,92 @@ def test_schedule_record_and_pick_fastest():
     for a, b in zip(tuned, plain):
         assert a["losses"] == pytest.approx(b["losses"], abs=1e-6)
     assert all(r["cands"] is None for r in plain)
+
+
+def _saved_partition_worker(rank, world, tmp):
+    import os
+
+    import torch.nn as nn
+    import torch.nn.functional as F
+
+    import smdistributed_modelparallel_b200 as smp
+    from smdistributed_modelparallel_b200.backend.exceptions import StepFunctionCalledError
+
+    class Net(nn.Module):
+        def __init__(self, dim=16):
+            super().__init__()
+            self.lin0_0, self.lin0_1, self.lin0_2 = nn.Linear(dim, dim), nn.Linear(dim, dim), nn.Linear(dim, dim)
+            self.lin1, self.lin2, self.lin3 = nn.Linear(dim, dim), nn.Linear(dim, dim), nn.Linear(dim, 10)
+
+        def forward(self, x):
+            for m in (self.lin0_0, self.lin0_1, self.lin0_2, self.lin1, self.lin2):
+                x = m(x)
+            return self.lin3(x)
+
+    @smp.step
+    def train_step(model, x, y):
+        loss = F.cross_entropy(model(x), y)
+        model.backward(loss)
+        return loss
+
+    want = {"lin0_0": 0, "lin0_1": 0, "lin0_2": 0, "lin1": 1, "lin2": 2, "lin3": 3}
+
+    def placed(model):
+        mm = smp.state.module_manager
+        return {n: mm.get_partition(getattr(model.module, n)) for n in want}
+
+    x, y = torch.randn(8, 16), torch.randint(0, 10, (8,))
+    out = {}
+    base = {"pipeline_parallel_degree": 4, "microbatches": 2, "ddp": False}
+    pfile = os.path.join(tmp, "partition.data")
+    # 1. manual partition; the assignment is also written to partition_file
+    smp.init({**base, "auto_partition": False, "default_partition": 0, "partition_file": pfile})
+    model = smp.DistributedModel(Net())
+    for n, r in want.items():
+        smp.set_partition(getattr(model.module, n), r)
+    train_step(model, x, y)
+    out["manual"] = placed(model)
+    info = smp.state.module_manager.get_model_partition_info()
+    smp.barrier()
+    out["file_written"] = os.path.exists(pfile)
+    # 2. the saved assignment wins over later set_partition calls; loading after a step is refused
+    smp.reset()
+    smp.init({**base, "auto_partition": False, "default_partition": 0})
+    model = smp.DistributedModel(Net())
+    model.load_saved_partition(info)
+    for n, r in {"lin0_0": 0, "lin0_1": 0, "lin0_2": 1, "lin1": 2, "lin2": 3, "lin3": 3}.items():
+        smp.set_partition(getattr(model.module, n), r)
+    train_step(model, x, y)
+    out["loaded_over_manual"] = placed(model)
+    try:
+        model.load_saved_partition(info)
+        out["refused_after_step"] = False
+    except StepFunctionCalledError:
+        out["refused_after_step"] = True
+    # 3. ... and over the auto-partitioner
+    smp.reset()
+    smp.init({**base, "auto_partition": True})
+    model = smp.DistributedModel(Net())
+    model.load_saved_partition(info)
+    train_step(model, x, y)
+    out["loaded_over_auto"] = placed(model)
+    # 4. config keys: load_partition + partition_file
+    smp.reset()
+    smp.init({**base, "auto_partition": True, "load_partition": True, "partition_file": pfile})
+    model = smp.DistributedModel(Net())
+    loss = train_step(model, x, y)
+    out["loaded_from_file"] = placed(model)
+    out["loss"] = loss.reduce_mean().item()
+    return out
+
+
+def test_saved_partition_is_reloaded(tmp_path):
+    """model.load_saved_partition(state.module_manager.get_model_partition_info()) and the load_partition /
+    partition_file config keys (reference test/torch/mpi_4ps/test_load_partition.py:60-136)."""
+    want = {"lin0_0": 0, "lin0_1": 0, "lin0_2": 0, "lin1": 1, "lin2": 2, "lin3": 3}
+    for r in run_distributed(_saved_partition_worker, 4, str(tmp_path), timeout=420):
+        assert r["manual"] == want and r["file_written"]
+        assert r["loaded_over_manual"] == want and r["refused_after_step"]
+        assert r["loaded_over_auto"] == want
+        assert r["loaded_from_file"] == want
+        assert r["loss"] == r["loss"]
