@@ -26,6 +26,41 @@ class TensorStub:
     requires_grad: bool
 
 
+def _walk(fn, obj):
+    """``map_structure`` that also descends into the attributes of plain Python objects (an instance of a user class
+    carrying tensors - reference torch/serialization.py:283-363 stubs those too, test/torch/test_serialization.py:13-26):
+    such an object is shallow-copied with its attributes mapped, the caller's instance is left untouched."""
+    import copy
+    import types
+    from collections.abc import Mapping
+
+    if torch.is_tensor(obj) or isinstance(obj, TensorStub):
+        return fn(obj)
+    if isinstance(obj, (list, tuple)) and not hasattr(obj, "smp_slice"):
+        mapped = [_walk(fn, o) for o in obj]
+        if isinstance(obj, tuple) and hasattr(obj, "_fields"):
+            return type(obj)(*mapped)
+        return type(obj)(mapped)
+    if isinstance(obj, Mapping):
+        try:
+            return type(obj)((k, _walk(fn, v)) for k, v in obj.items())
+        except TypeError:                       # a mapping class with its own constructor signature
+            new = copy.copy(obj)
+            for k, v in obj.items():
+                new[k] = _walk(fn, v)
+            return new
+    d = getattr(obj, "__dict__", None)
+    if isinstance(d, dict) and d and not isinstance(obj, (torch.nn.Module, type, types.ModuleType, types.FunctionType,
+                                                           types.MethodType, torch.dtype, torch.device)):
+        mapped = {k: _walk(fn, v) for k, v in d.items()}
+        if any(mapped[k] is not d[k] for k in d):
+            new = copy.copy(obj)
+            new.__dict__.update(mapped)
+            return new
+        return obj
+    return fn(obj)
+
+
 def stubify(obj):
     """Returns (skeleton, tensors): tensors replaced by stubs, listed in stub order."""
     tensors = []
@@ -36,16 +71,16 @@ def stubify(obj):
             return TensorStub(len(tensors) - 1, tuple(x.shape), x.dtype, bool(x.requires_grad))
         return x
 
-    return map_structure(f, obj), tensors
+    return _walk(f, obj), tensors
 
 
 def destubify(skel, tensors):
-    return map_structure(lambda x: tensors[x.index] if isinstance(x, TensorStub) else x, skel)
+    return _walk(lambda x: tensors[x.index] if isinstance(x, TensorStub) else x, skel)
 
 
 def stubs_of(skel):
     out = []
-    map_structure(lambda x: out.append(x) if isinstance(x, TensorStub) else None, skel)
+    _walk(lambda x: out.append(x) if isinstance(x, TensorStub) else x, skel)
     return sorted(out, key=lambda s: s.index)
 
 

@@ -222,3 +222,35 @@ def test_scheduler_takes_its_microbatch_order_from_the_pipeline_policy():
     # microbatch 0's backward starts as soon as its forward has ended, before microbatch 2's forward ends
     assert inter.index((0, "bwd")) < inter.index((2, "fwd_end"))
     assert sorted(e for e in inter if e[1] == "bwd") == [(0, "bwd"), (1, "bwd"), (2, "bwd")]
+
+
+def test_tensors_inside_plain_objects_are_stubbed():
+    """An instance of a user class that carries tensors crosses a stage boundary as the same class with stubs in place
+    of the tensors; the caller's instance is not modified (reference test/torch/test_serialization.py:13-40)."""
+    import torch
+
+    from smdistributed_modelparallel_b200.runtime.messages import TensorStub, destubify, stubify, stubs_of
+
+    class Holder:
+        def __init__(self, x):
+            self.tensor = torch.tensor([x])
+            self.name = "h"
+            self.inner = {"t": torch.ones(2, 3), "n": 3}
+
+    class Plain:
+        def __init__(self, x):
+            self.x = x
+
+    a = Holder(3.2)
+    skel, tensors = stubify(([a, Plain(5)], {"k": a.tensor}))
+    h = skel[0][0]
+    assert type(h) is Holder and isinstance(h.tensor, TensorStub) and isinstance(h.inner["t"], TensorStub)
+    assert h.name == "h" and h.inner["n"] == 3
+    assert isinstance(a.tensor, torch.Tensor) and isinstance(a.inner["t"], torch.Tensor)     # untouched
+    assert skel[0][1].x == 5 and len(tensors) == 3
+    assert [s.index for s in stubs_of(skel)] == [0, 1, 2] and stubs_of(skel)[1].shape == (2, 3)
+    back = destubify(skel, tensors)
+    assert torch.equal(back[0][0].tensor, a.tensor) and torch.equal(back[0][0].inner["t"], a.inner["t"])
+    assert back[1]["k"] is tensors[2]
+    import pickle
+    pickle.loads(pickle.dumps(stubify(({"k": torch.ones(1)},))[0]))                          # skeletons travel pickled
