@@ -77,7 +77,13 @@ def run_distributed(fn, world, *args, timeout=240, use_cuda=False):
         ctx = mp.get_context("spawn")
     else:
         ctx = mp.get_context("forkserver")
-        ctx.set_forkserver_preload(["torch", "numpy"])
+        # the HuggingFace modeling modules cost seconds to import; the server pays that once for every worker of the
+        # session (a module that is not installed is skipped by the fork server)
+        ctx.set_forkserver_preload(["torch", "numpy", "transformers", "transformers.models.gpt2.modeling_gpt2",
+                                    "transformers.models.gptj.modeling_gptj",
+                                    "transformers.models.gpt_neox.modeling_gpt_neox",
+                                    "transformers.models.gpt_neo.modeling_gpt_neo",
+                                    "transformers.models.bert.modeling_bert"])
     q = ctx.Queue()
     port = _free_port()
     env = dict(os.environ)

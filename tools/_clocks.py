@@ -33,3 +33,19 @@ def clocks(label, gpu_index=None, out=None):
     finally:
         rec = s.stop()
         print(f"clocks[{label}]: {json.dumps(rec)}", file=out or sys.stdout, flush=True)
+
+
+def calibrated_iters(fn, floor=10, target_s=0.25, cap=5000):
+    """How many back-to-back calls of ``fn`` fill ``target_s`` seconds (so that a timed loop is long enough for the
+    clock sampler to see the load): times three calls after the caller's warm-up."""
+    import torch
+
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(3):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    per = max(e0.elapsed_time(e1) / 3e3, 1e-6)
+    return int(min(cap, max(floor, target_s / per)))

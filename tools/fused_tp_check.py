@@ -58,16 +58,24 @@ dist.all_reduce(flag)
 log("NUMERICS", "PASS" if flag.item() == 0 else "FAIL")
 
 
-def timeit(fn, iters=10):
+def timeit(fn, iters=10, label="timed loop"):
+    """ms per call, max over ranks; the loop is long enough (~0.25 s, same count on every rank) for the clock
+    sampler, whose record (SM clock, throttle reasons during the loop) rank 0 prints next to the number."""
+    from tools._clocks import calibrated_iters, clocks
     for _ in range(3):
         fn()
+    n_it = torch.tensor([calibrated_iters(fn, floor=iters)], device=dev)
+    dist.all_reduce(n_it, op=dist.ReduceOp.MIN)
+    iters = int(n_it.item())
     torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-    e0.record()
-    for _ in range(iters):
-        fn()
-    e1.record()
-    torch.cuda.synchronize()
+    import contextlib
+    with (clocks(label) if dist.get_rank() == 0 else contextlib.nullcontext()):
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
     t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return t.item()

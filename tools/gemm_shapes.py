@@ -9,16 +9,19 @@ T, H, I, V, S, d, BH = 8192, 4096, 16384, 50400, 2048, 256, 64
 bf = torch.bfloat16
 
 
-def timeit(fn, iters=8):
+def timeit(fn, iters=8, label="timed loop"):
+    """ms per call over a ~0.25 s loop, with the clock record of that loop (SM clock, throttle reasons) printed."""
+    from tools._clocks import calibrated_iters, clocks
     for _ in range(3):
         fn()
-    torch.cuda.synchronize()
+    iters = calibrated_iters(fn, floor=iters)
     e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-    e0.record()
-    for _ in range(iters):
-        fn()
-    e1.record()
-    torch.cuda.synchronize()
+    with clocks(label):
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters
 
 

@@ -22,17 +22,26 @@ from smdistributed_modelparallel_b200.ops.gemm import gemm  # noqa: E402
 from smdistributed_modelparallel_b200.parallel.fused_tp import MAX_RANKS, SymmetricBuffer, _CommDesc, _ptr_array  # noqa: E402
 
 
-def timeit(fn, iters=10, warm=3):
+def timeit(fn, iters=10, warm=3, label="timed loop"):
+    """ms per call, max over ranks; the loop runs ~0.25 s (same count on every rank) and rank 0 prints the clock
+    record taken during it (SM clock, throttle reasons)."""
+    import contextlib
+
+    from tools._clocks import calibrated_iters, clocks
     for _ in range(warm):
         fn()
+    n_it = torch.tensor([calibrated_iters(fn, floor=iters)], device="cuda")
+    dist.all_reduce(n_it, op=dist.ReduceOp.MIN)
+    iters = int(n_it.item())
     torch.cuda.synchronize()
     dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(iters):
-        fn()
-    e1.record()
-    torch.cuda.synchronize()
+    with (clocks(label) if dist.get_rank() == 0 else contextlib.nullcontext()):
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
     t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t)
