@@ -26,33 +26,47 @@ class TensorStub:
     requires_grad: bool
 
 
-def _walk(fn, obj):
+def _walk(fn, obj, _active=None):
     """``map_structure`` that also descends into the attributes of plain Python objects (an instance of a user class
     carrying tensors - reference torch/serialization.py:283-363 stubs those too, test/torch/test_serialization.py:13-26):
-    such an object is shallow-copied with its attributes mapped, the caller's instance is left untouched."""
+    such an object is shallow-copied with its attributes mapped, the caller's instance is left untouched.  An object
+    met again while it is being walked (a reference cycle) is left as it is."""
     import copy
     import types
     from collections.abc import Mapping
 
     if torch.is_tensor(obj) or isinstance(obj, TensorStub):
         return fn(obj)
+    if obj is None or isinstance(obj, (int, float, str, bytes, bool)):
+        return fn(obj)
+    _active = set() if _active is None else _active
+    if id(obj) in _active:
+        return obj
+    _active.add(id(obj))
+    try:
+        return _walk_container(fn, obj, _active, copy, types, Mapping)
+    finally:
+        _active.discard(id(obj))
+
+
+def _walk_container(fn, obj, _active, copy, types, Mapping):
     if isinstance(obj, (list, tuple)) and not hasattr(obj, "smp_slice"):
-        mapped = [_walk(fn, o) for o in obj]
+        mapped = [_walk(fn, o, _active) for o in obj]
         if isinstance(obj, tuple) and hasattr(obj, "_fields"):
             return type(obj)(*mapped)
         return type(obj)(mapped)
     if isinstance(obj, Mapping):
         try:
-            return type(obj)((k, _walk(fn, v)) for k, v in obj.items())
+            return type(obj)((k, _walk(fn, v, _active)) for k, v in obj.items())
         except TypeError:                       # a mapping class with its own constructor signature
             new = copy.copy(obj)
             for k, v in obj.items():
-                new[k] = _walk(fn, v)
+                new[k] = _walk(fn, v, _active)
             return new
     d = getattr(obj, "__dict__", None)
     if isinstance(d, dict) and d and not isinstance(obj, (torch.nn.Module, type, types.ModuleType, types.FunctionType,
                                                            types.MethodType, torch.dtype, torch.device)):
-        mapped = {k: _walk(fn, v) for k, v in d.items()}
+        mapped = {k: _walk(fn, v, _active) for k, v in d.items()}
         if any(mapped[k] is not d[k] for k in d):
             new = copy.copy(obj)
             new.__dict__.update(mapped)

@@ -254,3 +254,20 @@ def test_tensors_inside_plain_objects_are_stubbed():
     assert back[1]["k"] is tensors[2]
     import pickle
     pickle.loads(pickle.dumps(stubify(({"k": torch.ones(1)},))[0]))                          # skeletons travel pickled
+
+
+def test_stubbing_survives_reference_cycles():
+    import torch
+
+    from smdistributed_modelparallel_b200.runtime.messages import TensorStub, stubify
+
+    class Node:
+        def __init__(self):
+            self.t = torch.ones(2)
+            self.me = self                      # a cycle through an attribute
+            self.peers = [self]
+
+    n = Node()
+    skel, tensors = stubify({"n": n, "again": n})
+    assert len(tensors) == 2                    # the object is reached twice from the top, each time walked once
+    assert isinstance(skel["n"].t, TensorStub) and skel["n"].me is n and skel["n"].peers[0] is n
