@@ -34,7 +34,7 @@ def test_example_tp2_pp2_checkpoint_and_resume():
     for a, s in zip(again, straight):
         assert a["start"] == 4                                   # newest checkpoint: step 4
         # resumed steps 4 and 5 equal steps 4 and 5 of an uninterrupted run (weights and Adam state restored)
-        assert a["losses"] == pytest.approx(s["losses"][4:6], abs=2e-5), (a["losses"], s["losses"])
+        assert a["losses"] == pytest.approx(s["losses"][4:6], abs=1e-4), (a["losses"], s["losses"])
 
 
 def test_example_sharded_data_parallel_with_checkpointing():

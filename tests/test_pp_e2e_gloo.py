@@ -143,7 +143,7 @@ def test_pp2_toy_networks_match_single_process(kind, auto):
     for r in res:
         assert r["parts"] == [0, 1], r["parts"]
         for a, b in zip(r["losses"], want):
-            assert abs(a - b) < 1e-5, (r["losses"], want)
+            assert abs(a - b) < 5e-5, (r["losses"], want)
     full = res[0]["sd"]
     for k, v in ref.state_dict().items():
         assert k in full, k

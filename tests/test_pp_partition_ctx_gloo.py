@@ -118,7 +118,7 @@ def test_partition_contexts_place_modules_and_gradients_match(kind):
     res = run_distributed(_worker, 2, kind, timeout=300)
     for r in res:
         assert r["placed"] == r["want"], (r["placed"], r["want"])
-        assert abs(r["loss"] - r["oracle"]) < 1e-6 and r["worst"] < 1e-6, r
+        assert abs(r["loss"] - r["oracle"]) < 5e-6 and r["worst"] < 5e-6, r
     if kind == "one_stage":
         assert res[1]["n_local"] == 0 and res[0]["hops"] <= 1      # only the step's output travels to the idle stage
     else:
