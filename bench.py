@@ -66,6 +66,23 @@ def reference_arm(args):
     return 0
 
 
+def _roofline(model_tflops):
+    """Model TFLOP/s per GPU against the measured cuBLAS bf16 throughput of this pod (driver-written
+    MEASURED_PEAKS.json; B200_PROFILING.md's stated numbers when the file is absent)."""
+    peaks = {"bf16_tflops": 1664.2, "bf16_tflops_sustained": 1351.7, "source": "fallback (B200_PROFILING.md)"}
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            m = json.load(f)
+        peaks = {"bf16_tflops": float(m["bf16_tflops"]), "bf16_tflops_sustained": float(m["bf16_tflops_sustained"]),
+                 "source": "MEASURED_PEAKS.json"}
+    except (OSError, ValueError, KeyError):
+        pass
+    return {"cublas_bf16_tflops_burst": peaks["bf16_tflops"], "cublas_bf16_tflops_sustained": peaks["bf16_tflops_sustained"],
+            "fraction_of_sustained": round(model_tflops / peaks["bf16_tflops_sustained"], 3),
+            "fraction_of_burst": round(model_tflops / peaks["bf16_tflops"], 3), "peaks_from": peaks["source"]}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled during the timed region."""
 
@@ -301,6 +318,7 @@ def run_product(args, model_name, parallelism, steps, warmup, micro=0, nmb=0, ch
                        "valid": not bool(args.layers)},
             "model_tflops_per_gpu": round(value * flops / n / 1e12, 1),
             "model_tflops_note": "6 x matmul params + full (non-causal) attention products per token; the kernels skip the masked half of causal attention",
+            "roofline": _roofline(value * flops / n / 1e12),
             "clocks": clocks,
             "e2e": {"value": round(e2e, 1), "unit": "tokens/s", "h2d_bytes_per_step": per_rank_batch * seq * 8,
                     "d2h_bytes_per_step": 4 * nmb, "ms_per_step": round(ms_b, 2), "last_loss": last, "losses": seen[-8:]},

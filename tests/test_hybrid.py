@@ -5,8 +5,8 @@ gradient, so this is the gradient comparison of the reference's tier (reference 
 test_gpt_grad.py:88-193, test_opt_sharding.py:15-17, test_zero.py:40-76).
 
 The matrix runs on CPU / gloo in the default tier (four processes) and, unchanged, on four GPUs over NCCL under
-``-m gpu`` - there the 16-bit cases go through the tcgen05 GEMMs, the flash attention kernels, the fused
-tensor-parallel collectives and the peer-memory ZeRO-3 kernels.
+``-m gpu`` with ``SMP_RUN_HYBRID_GPU=1`` - there the 16-bit cases go through the tcgen05 GEMMs, the flash attention
+kernels, the fused tensor-parallel collectives and the peer-memory ZeRO-3 kernels.
 """
 
 import pytest
@@ -163,4 +163,9 @@ def test_hybrid_layouts_track_dense_on_gloo(name):
 def test_hybrid_layouts_track_dense_on_gpus(name):
     if torch.cuda.device_count() < 4:
         pytest.skip("needs 4 GPUs")
+    import os
+    if os.environ.get("SMP_RUN_HYBRID_GPU", "0") != "1":
+        # the matrix has run on gloo only so far (this round's multi-GPU budget was spent before it existed); until a
+        # 4-GPU log of it is under profiles/, a -m gpu run on a larger box does not meet it unannounced
+        pytest.skip("set SMP_RUN_HYBRID_GPU=1 to run the hybrid matrix on GPUs")
     _check(name, run_distributed(_worker, 4, name, True, timeout=900, use_cuda=True))
