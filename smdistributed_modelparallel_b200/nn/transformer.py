@@ -13,8 +13,10 @@ Execution differs from the reference by design (B200-first):
   all-gather tokens first, row-parallel GEMMs reduce-scatter after (``parallel/tp_ops.py``), so
   LayerNorm / dropout / residual touch 1/t of the tokens and no all-reduce remains;
 * q, k, v are one fused GEMM on the tcgen05 kernel (the three reference Linear modules survive as
-  state-dict names only), bias+GELU is a GEMM epilogue, rotary is fused into the QKV split,
-  softmax is the native causal/masked kernel with no 2048-key limit.
+  state-dict names only), bias+GELU is a GEMM epilogue, rotary is fused into the QKV split, and the attention core
+  (scores, masks, softmax, dropout, context) is one flash-style kernel pair with no length limit and no
+  ``S x S`` tensor (``ops/attention.py``, ``csrc/kernels/sm100/attention.cu``);
+* ``optimize: memory`` selects the reference's other layout instead (hidden-sharded activations, ``_forward_memory``).
 """
 
 from __future__ import annotations
