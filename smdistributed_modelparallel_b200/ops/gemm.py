@@ -23,8 +23,8 @@ _EPI_BY_NAME = {"none": EPI_NONE, "gelu_tanh": EPI_GELU_TANH, "gelu_erf": EPI_GE
 
 _TRI = {None: 0, "lower_out": 1, "lower_a": 2, "lower_at": 3}
 
-# diagnostics: how many GEMMs ran natively / fell back to torch.matmul (shape or alignment limits)
-stats = {"native": 0, "fallback": 0}
+# diagnostics: how many GEMMs ran natively / ran natively on re-packed operands (alignment) / fell back to torch.matmul
+stats = {"native": 0, "fallback": 0, "padded": 0}
 
 # gathers deferred to the GEMM that first reads a sharded unit's weight (parallel/sdp_fused.py)
 from ._sdp_hook import pending_gathers as _sdp_pending  # noqa: E402
@@ -91,6 +91,36 @@ def _native_ok(a, b, out, residual, bias):
     return True
 
 
+def aligned_operands(a, b, a_mn_major, b_mn_major):
+    """Operands whose rows are not 16-byte multiples (a head count or hidden size that is not a multiple of 8 on this
+    rank - the reference's own uneven-split case is H = 845 over 13 heads, test/torch/mpi_4ps/test_dist_modules.py:
+    81-130) cannot be addressed by TMA.  Re-pack both as K-major ``[..., rows, K8]`` with the reduction dimension
+    zero-padded to the next multiple of 8: the zeros add nothing to the products, M and N are unchanged, so output,
+    bias, residual and epilogue are untouched."""
+    A = a.transpose(-1, -2) if a_mn_major else a
+    B = b.transpose(-1, -2) if b_mn_major else b
+    K = A.shape[-1]
+    K8 = (K + 7) // 8 * 8
+    Ap = A.new_zeros(A.shape[:-1] + (K8,))
+    Bp = B.new_zeros(B.shape[:-1] + (K8,))
+    Ap[..., :K] = A
+    Bp[..., :K] = B
+    return Ap, Bp
+
+
+_pad_state = {"checked": False, "ok": True}
+
+
+def _misaligned_only(a, b, out, residual, bias):
+    """True when re-packing the operands is all it takes to get onto the native kernel."""
+    if not a.is_cuda or a.dtype not in (torch.bfloat16, torch.float16) or b.dtype != a.dtype:
+        return False
+    for t in (out, residual):
+        if t is not None and t.stride(-1) != 1:
+            return False
+    return bias is None or bias.is_contiguous()
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
          out: torch.Tensor | None = None, out_dtype: torch.dtype | None = None, bias: torch.Tensor | None = None,
          residual: torch.Tensor | None = None, alpha: float = 1.0, beta: float = 1.0, epilogue: str | int = "none",
@@ -129,6 +159,26 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
         gather(None)                 # cannot fuse into this GEMM: gather the unit now, stand-alone
         gather = None
     if not _native_ok(a, b, out, residual, bias):
+        if _pad_state["ok"] and tri == 0 and _misaligned_only(a, b, out, residual, bias):
+            Ap, Bp = aligned_operands(a, b, a_mn_major, b_mn_major)
+            if _native_ok(Ap, Bp, out, residual, bias):
+                res = gemm(Ap, Bp, out=out, out_dtype=out_dtype, bias=bias, residual=residual, alpha=alpha, beta=beta,
+                           epilogue=epi, aux_out=aux_out)
+                if not _pad_state["checked"] and residual is not out:
+                    # first use in this process (with inputs the call did not overwrite): hold the re-packed path
+                    # against the fp32 formulation once; on disagreement say so and stay on torch.matmul
+                    _pad_state["checked"] = True
+                    chk = _reference(a, b, a_mn_major, b_mn_major, torch.float32, bias, residual, alpha, beta, epi, None)
+                    err = (res.float() - chk).abs().max().item() / (chk.abs().max().item() + 1e-6)
+                    if not err < 3e-2:
+                        from ..backend.logger import get_logger
+                        get_logger().error(f"re-packed GEMM operands disagree with the fp32 formulation (rel {err:.3e}); "
+                                           "odd-shaped GEMMs use torch.matmul from now on")
+                        _pad_state["ok"] = False
+                        res = None
+                if res is not None:
+                    stats["padded"] += 1
+                    return res
         if a.is_cuda:
             stats["fallback"] += 1
         res = _reference(a, b, a_mn_major, b_mn_major, out_dtype, bias, residual, alpha, beta, epi, aux_out)

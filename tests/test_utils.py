@@ -102,3 +102,27 @@ def test_rng_manager_leaves_the_global_generators_alone():
     assert not torch.equal(a, b)                                # the side stream advances between blocks
     with mgr.consistent_rng_state(seed=99):
         assert torch.equal(torch.rand(3), a)                    # reseeding restarts it
+
+
+def test_gemm_operand_repacking_keeps_the_product():
+    """ops.gemm.aligned_operands: K-major copies with the reduction dimension zero-padded to a multiple of 8 give the
+    same product for every storage layout, 2-D and batched (the re-packed operands are what the tcgen05 kernel gets
+    when a row is not a 16-byte multiple)."""
+    import torch
+
+    from smdistributed_modelparallel_b200.ops.gemm import aligned_operands, gemm
+
+    torch.manual_seed(0)
+    for batch in ((), (3,)):
+        A, B = torch.randn(*batch, 5, 13), torch.randn(*batch, 7, 13)
+        want = A @ B.transpose(-1, -2)
+        for a_mn in (False, True):
+            for b_mn in (False, True):
+                a = A.transpose(-1, -2).contiguous() if a_mn else A
+                b = B.transpose(-1, -2).contiguous() if b_mn else B
+                Ap, Bp = aligned_operands(a, b, a_mn, b_mn)
+                assert Ap.shape == (*batch, 5, 16) and Bp.shape == (*batch, 7, 16)
+                assert Ap.is_contiguous() and Bp.is_contiguous()
+                assert torch.allclose(Ap @ Bp.transpose(-1, -2), want, atol=1e-6)
+                # on CPU the front-end answers with the plain formulation, whatever the alignment
+                assert torch.allclose(gemm(a, b, a_mn_major=a_mn, b_mn_major=b_mn), want, atol=1e-5)
