@@ -96,7 +96,32 @@ at::Tensor scatter_and_merge(const PG& pg, const at::Tensor& x, int64_t split_di
     off += in_splits[k];
   }
   auto out_flat = at::empty({prefix(out_splits, n)}, x.options());
-  wait_work(pg->alltoall_base(out_flat, in_flat, out_splits, in_splits));
+  if (x.is_cuda()) {
+    wait_work(pg->alltoall_base(out_flat, in_flat, out_splits, in_splits));  // NCCL: one grouped send / recv
+  } else {
+    // gloo: pairwise transfers.  Its all-to-all blocks against any other collective in flight on the same group (an
+    // asynchronous gradient all-reduce launched earlier in the same backward pass deadlocked it one run in ten),
+    // point-to-point transfers do not.
+    std::vector<WorkPtr> works;
+    int64_t ooff = 0, ioff = 0;
+    for (int64_t k = 0; k < n; ++k) {
+      if (k == r) {
+        if (out_splits[k] > 0) out_flat.narrow(0, ooff, out_splits[k]).copy_(in_flat.narrow(0, ioff, in_splits[k]));
+      } else {
+        if (out_splits[k] > 0) {
+          std::vector<at::Tensor> v{out_flat.narrow(0, ooff, out_splits[k])};
+          works.push_back(pg->recv(v, (int)k, 0));
+        }
+        if (in_splits[k] > 0) {
+          std::vector<at::Tensor> v{in_flat.narrow(0, ioff, in_splits[k])};
+          works.push_back(pg->send(v, (int)k, 0));
+        }
+      }
+      ooff += out_splits[k];
+      ioff += in_splits[k];
+    }
+    for (auto& w : works) wait_work(w);
+  }
   std::vector<at::Tensor> pieces;
   pieces.reserve(n);
   off = 0;

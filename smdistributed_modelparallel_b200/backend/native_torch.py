@@ -17,8 +17,11 @@ _PATH = Path(__file__).resolve().parent.parent / "lib" / "_smpb200_torch.so"
 _mod = None
 
 
-def enabled() -> bool:
-    return os.environ.get("SMP_NATIVE_COMM", "1") != "0"
+def enabled(part: str | None = None) -> bool:
+    """``SMP_NATIVE_COMM=0`` switches the whole runtime off; ``SMP_NATIVE_COMM_OFF=a2a,reducer,p2p`` single parts."""
+    if os.environ.get("SMP_NATIVE_COMM", "1") == "0":
+        return False
+    return part is None or part not in os.environ.get("SMP_NATIVE_COMM_OFF", "").split(",")
 
 
 def load():

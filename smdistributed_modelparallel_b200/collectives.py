@@ -46,7 +46,7 @@ def allgatherv_tensor(tensor: torch.Tensor, counts, group=CommGroup.DP_GROUP) ->
     if n == 1:
         return tensor
     from .backend import native_torch
-    if native_torch.enabled() and flat.is_contiguous():
+    if native_torch.enabled("a2a") and flat.is_contiguous():
         native_torch.load().allgatherv(pg, flat, counts)          # csrc/torch_ext/comm_runtime.cpp
         return tensor
     r = dist.get_rank(pg)

@@ -175,7 +175,7 @@ class GradReducer:
         from ..backend import native_torch
 
         gb = self.grad_buffer
-        if gb is None or not native_torch.enabled() or getattr(self, "_native_broken", False):
+        if gb is None or not native_torch.enabled("reducer") or getattr(self, "_native_broken", False):
             return None
         key = (id(gb), gb.buffer.data_ptr())
         if getattr(self, "_native_key", None) != key:
@@ -335,7 +335,7 @@ class GradReducer:
             if group is None or dist.get_world_size(group) == 1:
                 return
             from ..backend import native_torch
-            if native_torch.enabled():
+            if native_torch.enabled("reducer"):
                 b["work"] = native_torch.load().FlatBucket(group, [q.grad for q in b["params"]])
                 b["flat"] = None
                 self.stats["overlapped_elems"] += b["work"].numel()

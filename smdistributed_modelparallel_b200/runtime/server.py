@@ -169,7 +169,7 @@ class PipelineP2P:
         mode = os.environ.get("SMP_NATIVE_P2P", "auto")
         on_gloo = dist.is_initialized() and dist.get_backend() == "gloo"
         self._engine = native_torch.load().P2PEngine() if (
-            native_torch.enabled() and (mode == "1" or (mode == "auto" and on_gloo))) else None
+            native_torch.enabled("p2p") and (mode == "1" or (mode == "auto" and on_gloo))) else None
         self._recv_stream = None
         dev = getattr(state, "device", None)
         if dev is not None and dev.type == "cuda" and os.environ.get("SMP_P2P_SIDE_STREAM", "0") == "1":

@@ -57,10 +57,12 @@ def _entry(rank, world, port, fn, args, queue, use_cuda=False, env=None):
         # tiny tensors, several ranks per machine: intra-op threads only fight one another
         torch.set_num_threads(max(1, (os.cpu_count() or 4) // (2 * world)))
     sys.path.insert(0, ROOT)
+    import faulthandler
+    faulthandler.enable()                    # a crash inside native code leaves the Python stack of every thread
     dump_after = float(os.environ.get("SMP_TEST_HANG_DUMP_S", "0"))
     if dump_after > 0:                       # where is every thread if the worker is still running by then?
         import faulthandler
-        faulthandler.dump_traceback_later(dump_after, exit=True)
+        faulthandler.dump_traceback_later(dump_after, exit=os.environ.get("SMP_TEST_HANG_DUMP_NOEXIT", "0") != "1")
     try:
         out = _to_wire(fn(rank, world, *args))
         queue.put((rank, "ok", out))
@@ -92,8 +94,25 @@ def run_distributed(fn, world, *args, timeout=240, use_cuda=False):
         p.start()
     results = {}
     try:
-        for _ in range(world):
-            rank, status, payload = q.get(timeout=timeout)
+        import queue
+        import time
+        deadline = time.monotonic() + timeout
+        while len(results) < world:
+            try:
+                rank, status, payload = q.get(timeout=1.0)
+            except queue.Empty:
+                # a worker that died without reporting (a crash in native code, a kill) will never answer: say which
+                # one and how it ended instead of waiting out the whole timeout
+                dead = [(r, p.exitcode) for r, p in enumerate(procs)
+                        if p.exitcode not in (None, 0) and r not in results]
+                if dead:
+                    time.sleep(1.0)                      # let a result that was already on its way arrive
+                    if q.empty():
+                        raise AssertionError(f"worker(s) died without a result (rank, exit code): {dead}") from None
+                if time.monotonic() > deadline:
+                    raise AssertionError(f"no result from ranks {sorted(set(range(world)) - set(results))} "
+                                         f"within {timeout:.0f} s") from None
+                continue
             if status != "ok":
                 raise AssertionError(f"rank {rank} failed:\n{payload}")
             results[rank] = _from_wire(payload)
