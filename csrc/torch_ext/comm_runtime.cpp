@@ -97,7 +97,16 @@ at::Tensor scatter_and_merge(const PG& pg, const at::Tensor& x, int64_t split_di
   }
   auto out_flat = at::empty({prefix(out_splits, n)}, x.options());
   if (x.is_cuda()) {
-    wait_work(pg->alltoall_base(out_flat, in_flat, out_splits, in_splits));  // NCCL: one grouped send / recv
+    // NCCL: one grouped send / recv over per-peer views of the two flat buffers
+    std::vector<at::Tensor> outs, ins;
+    int64_t ooff = 0, ioff = 0;
+    for (int64_t k = 0; k < n; ++k) {
+      outs.push_back(out_flat.narrow(0, ooff, out_splits[k]));
+      ins.push_back(in_flat.narrow(0, ioff, in_splits[k]));
+      ooff += out_splits[k];
+      ioff += in_splits[k];
+    }
+    wait_work(pg->alltoall(outs, ins));
   } else {
     // gloo: pairwise transfers.  Its all-to-all blocks against any other collective in flight on the same group (an
     // asynchronous gradient all-reduce launched earlier in the same backward pass deadlocked it one run in ten),

@@ -10,8 +10,8 @@ collectives.py:214-245, expected results pinned by test/torch/mpi_4ps/test_colle
   (remainder spread over the first ranks), exchange slices all-to-all, concatenate the received slices along
   ``merge_axis``: rank i ends up with the i-th slice of every rank.
 
-Both run in the native tensor-communication runtime (``csrc/torch_ext/comm_runtime.cpp``: one uneven all-to-all /
-padded all-gather over flat buffers through the c10d process group - NCCL on GPUs, gloo on CPU); ``SMP_NATIVE_COMM=0``
+Both run in the native tensor-communication runtime (``csrc/torch_ext/comm_runtime.cpp``: flat send / receive buffers and one grouped all-to-all /
+padded all-gather through the c10d process group - NCCL on GPUs, gloo on CPU); ``SMP_NATIVE_COMM=0``
 selects the ``torch.distributed`` formulation below instead.
 """
 

@@ -283,7 +283,7 @@ def _all_to_all_impl(x, split_dim, merge_dim, split_shapes=None, merge_shapes=No
         merge_shapes = [int(v) for v in allm.tolist()]
     from ..backend import native_torch
     if native_torch.enabled("a2a"):
-        # one uneven all-to-all over flat buffers in the native runtime (csrc/torch_ext/comm_runtime.cpp)
+        # flat send / receive buffers and one grouped all-to-all in the native runtime (csrc/torch_ext/comm_runtime.cpp)
         return _throttled(native_torch.load().scatter_and_merge, group, x, split_dim, merge_dim,
                           [int(v) for v in s_shapes], [int(v) for v in merge_shapes])
     sends = [p.contiguous() for p in torch.split(x, s_shapes, dim=split_dim)]
