@@ -45,6 +45,15 @@ def _from_wire(obj):
     return obj
 
 
+def _orderly_shutdown(success):
+    mod = sys.modules.get("smdistributed_modelparallel_b200")
+    try:
+        if mod is not None and mod.state.core is not None:
+            mod.state.core.shutdown(success)
+    except Exception:                        # noqa: BLE001 - teardown must not mask the test's own result
+        pass
+
+
 def _entry(rank, world, port, fn, args, queue, use_cuda=False, env=None):
     if env:                                  # a fork-server child starts from the server's environment
         os.environ.update(env)
@@ -69,6 +78,11 @@ def _entry(rank, world, port, fn, args, queue, use_cuda=False, env=None):
     except Exception:
         queue.put((rank, "err", traceback.format_exc()))
         raise
+    finally:
+        # a multiprocessing child leaves through os._exit: no atexit handlers, so the library's orderly shutdown
+        # (flush pending control messages, tell the peers goodbye) has to be called here - without it the peers see
+        # this rank's sockets close unannounced, which the message bus reports as a lost peer
+        _orderly_shutdown(sys.exc_info()[0] is None)
 
 
 def run_distributed(fn, world, *args, timeout=240, use_cuda=False):
