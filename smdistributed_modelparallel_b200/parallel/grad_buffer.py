@@ -374,9 +374,17 @@ class GradReducer:
             return
         native = self._native_reducer()
         if native is not None:
-            for region, a, b in self.buckets[idx]["ranges"]:
-                native.launch(self._native_ids[region], int(a), int(b))
-            return
+            try:
+                for region, a, b in self.buckets[idx]["ranges"]:
+                    native.launch(self._native_ids[region], int(a), int(b))
+                return
+            except Exception as e:          # noqa: BLE001
+                if native.in_flight():      # part of this step is already on its way through the native path
+                    raise
+                from ..backend.logger import get_logger
+                get_logger().error(f"native bucket reducer failed at its first launch ({type(e).__name__}: {e}); "
+                                   "reducing gradients through torch.distributed calls from Python instead")
+                self._native_broken, self._native_key = True, None
         buf = self.grad_buffer.buffer
         for region, a, b in self.buckets[idx]["ranges"]:
             group = self._group_of(region)
