@@ -59,6 +59,8 @@ def _worker(rank, world, cuda=False):
     got_a = eng.get_ready_tensor(hr1)
     eng.wait(hs1)
     eng.wait(hs2)
+    if cuda:
+        torch.cuda.synchronize()            # NCCL's wait orders streams; completion needs the kernels to have run
     assert eng.poll(hs1) and eng.poll(hr1)
     out["p2p"] = (got_a.clone(), got_b.clone(), got_a.data_ptr() == ra.data_ptr())
     st = eng.stats()
