@@ -138,6 +138,7 @@ class ShardedDataParallelEngine:
         self.dynamic = False
         self.overflow = False
         self._built = False
+        self.gather_stats = {"prefetched": 0, "on_demand": 0}      # units gathered ahead of use / when first needed
         self._order = []             # unit execution order observed in the first forward
         self._order_frozen = False
         self._pending_reduce = []    # (work, tmp_shard, unit, full_grad)
@@ -300,6 +301,8 @@ class ShardedDataParallelEngine:
 
     def _ensure(self, u: Unit, lazy_ok=False):
         if u.full is None:
+            if u.gather_work is None and not u.lazy_pending and getattr(u, "_pending_full", None) is None:
+                self.gather_stats["on_demand"] += 1
             self._issue_gather(u, lazy_ok)
             if u.gather_work is not None:
                 if self.fused:
@@ -339,7 +342,10 @@ class ShardedDataParallelEngine:
             nxt = self._order[j]
             if self.fused and nxt.first_weight is not None and (direction > 0 or nxt.recompute_seen):
                 return          # gathered from inside its own first GEMM
-            if nxt.full is None and nxt.numel <= self.max_live:
+            # sdp_max_live_parameters: a unit larger than the budget is never fetched ahead of its use
+            if nxt.full is None and nxt.gather_work is None and not nxt.lazy_pending and \
+                    getattr(nxt, "_pending_full", None) is None and nxt.numel <= self.max_live:
+                self.gather_stats["prefetched"] += 1
                 self._issue_gather(nxt)
 
     def _pre_forward(self, units, args=None):

@@ -339,3 +339,57 @@ def test_stock_hf_gpt2_with_tied_embeddings_under_sdp(unit_elements, min_units):
     res = run_distributed(_hf_sdp_worker, 2, unit_elements, timeout=300)
     for r in res:
         assert r["units"] >= min_units and r["worst"] < 1e-5, r
+
+
+def _knob_worker(rank, world, max_live, hierarchical):
+    import copy
+
+    import smdistributed_modelparallel_b200 as smp
+
+    os.environ["SMP_SDP_UNIT_ELEMENTS"] = "9000"
+    smp.init({"sharded_data_parallel_degree": 2, "microbatches": 2, "ddp": True, "sdp_param_persistence_threshold": 100,
+              "sdp_max_live_parameters": max_live, "sdp_hierarchical_allgather": hierarchical})
+    torch.manual_seed(3)
+    module = smp.nn.DistributedTransformerLMHead(**CFG)
+    oracle = copy.deepcopy(module)
+    model = smp.DistributedModel(module)
+    opt = smp.DistributedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.0))
+    oopt = torch.optim.AdamW(oracle.parameters(), lr=1e-2, weight_decay=0.0)
+
+    @smp.step
+    def train_step(model, ids):
+        loss, _ = model((ids, None, None, None, ids))
+        model.backward(loss)
+        return loss
+
+    torch.manual_seed(5)
+    all_ids = torch.randint(0, CFG["vocab_size"], (3, 4 * world, 16))
+    for it in range(3):
+        opt.zero_grad()
+        train_step(model, all_ids[it, rank * 4:(rank + 1) * 4])
+        opt.step()
+        oopt.zero_grad()
+        ol, _ = oracle((all_ids[it], None, None, None, all_ids[it]))
+        ol.backward()
+        torch.nn.utils.clip_grad_norm_(oracle.parameters(), 1.0)
+        oopt.step()
+    full, osd = model.state_dict(), oracle.state_dict()
+    worst = max((full[k].float() - osd[k]).abs().max().item() for k in osd if k in full)
+    eng = model.sdp_engine
+    return {"worst": worst, "stats": dict(eng.gather_stats), "units": len(eng.units), "max_live": eng.max_live,
+            "hierarchical": eng.hierarchical, "largest": max(u.numel for u in eng.units)}
+
+
+def test_sdp_max_live_parameters_bounds_prefetching():
+    """``sdp_max_live_parameters`` (reference backend/ds_config_defaults.json:14, DeepSpeed's stage3_max_live_parameters):
+    with the default budget the next unit is fetched while the current one computes; a budget smaller than a unit
+    switches the look-ahead off - every unit is then gathered when first needed - and the numbers do not change.
+    ``sdp_hierarchical_allgather`` is accepted and, inside one node, changes nothing."""
+    ahead = run_distributed(_knob_worker, 2, 10 ** 9, True)
+    lazy = run_distributed(_knob_worker, 2, 1, False)
+    for a, b in zip(ahead, lazy):
+        assert a["units"] >= 3 and a["stats"]["prefetched"] > 0
+        assert b["max_live"] == 1 < b["largest"] and b["stats"]["prefetched"] == 0
+        assert b["stats"]["on_demand"] > a["stats"]["on_demand"]
+        assert a["hierarchical"] is True and b["hierarchical"] is False
+        assert a["worst"] < 2e-3 and abs(a["worst"] - b["worst"]) < 1e-6
