@@ -489,7 +489,13 @@ SMPC_API int smpc_bus_shutdown(int success) {
       const uint64_t target = b->tx_enqueued;
       b->tx_cv.wait_for(tl, std::chrono::seconds(5), [&] { return b->tx_done >= target; });
     }
-    b->stop.store(true);
+    {
+      // under the sender's mutex: a sender that has just found its queue empty must either see the flag or be
+      // asleep when the notification comes - set outside the lock, the wake-up could fall between the two and
+      // the join below would wait for ever
+      std::lock_guard<std::mutex> tl(b->tx_mu);
+      b->stop.store(true);
+    }
     b->tx_cv.notify_all();
     if (b->tx.joinable()) b->tx.join();
     if (b->rx.joinable()) b->rx.join();
