@@ -498,12 +498,13 @@ SMPC_API int smpc_bus_shutdown(int success) {
     }
     b->tx_cv.notify_all();
     if (b->tx.joinable()) b->tx.join();
+    // everything this rank had to say is on the wire: end the connections, which also wakes the receiver should it
+    // be in the middle of a frame whose sender has stalled, then wait for it
+    for (int fd : b->fds)
+      if (fd >= 0) ::shutdown(fd, SHUT_RDWR);
     if (b->rx.joinable()) b->rx.join();
     for (int fd : b->fds)
-      if (fd >= 0) {
-        ::shutdown(fd, SHUT_RDWR);
-        ::close(fd);
-      }
+      if (fd >= 0) ::close(fd);
   }
   if (b->listen_fd >= 0) ::close(b->listen_fd);
   delete b;
