@@ -552,7 +552,13 @@ class ExecutionServer:
         borrowed = []
         meta_bytes = sum(p.numel() * p.element_size() for p in root.parameters() if p.is_meta)
         if meta_bytes:
-            limit = float(os.environ.get("SMP_TRACE_MAX_BYTES", 60e9))
+            # trace_device="cpu" (reference model.py:111-124): the traced passes run on the host - for models whose
+            # unpartitioned parameters do not fit one GPU; the budget is then the host's (SMP_TRACE_MAX_BYTES_CPU)
+            on_cpu = getattr(model, "trace_device", "gpu") == "cpu"
+            if on_cpu:
+                dev = torch.device("cpu")
+            limit = float(os.environ.get("SMP_TRACE_MAX_BYTES_CPU", 400e9)) if on_cpu else \
+                float(os.environ.get("SMP_TRACE_MAX_BYTES", 60e9))
             if meta_bytes > limit:          # a size rule, so that every leader takes the same decision
                 get_logger().info(f"tracing skipped: {meta_bytes / 1e9:.1f} GB of parameters are not materialised "
                                   f"(limit {limit / 1e9:.0f} GB)")
@@ -608,17 +614,26 @@ class ExecutionServer:
         st.is_tracing_flag = True
         prev_mb = st.microbatch
         st.microbatch = 0
+        failed = None
         try:
             with torch.no_grad():
                 for i in range(passes):
                     state_["timed"] = i              # 0: warm-up; 1: first timed pass (also sizes); 2..: timing only
                     step_fn.func(*a, **k)
+        except Exception as e:                       # noqa: BLE001 - tracing is an aid: partition untraced instead
+            failed = e
         finally:
             st.is_tracing_flag = False
             st.microbatch = prev_mb
             for h in hooks:
                 h.remove()
             self._return_storage(borrowed)
+        if failed is not None:
+            get_logger().warning(f"first-step tracing failed ({type(failed).__name__}: {failed}); the model is "
+                                 "partitioned from the untraced estimates")
+            trace.times.clear()
+            trace.memory.clear()
+            return None, None
         times = {mm.get_module(n): t for n, t in trace.times.items()} if want_t else None
         memory = {mm.get_module(n): float(b) for n, b in trace.memory.items()} if want_m else None
         return times, memory

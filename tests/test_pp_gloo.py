@@ -283,7 +283,7 @@ def test_pp2_dp2_bf16_with_activation_checkpointing():
         assert torch.equal(v, other["after"][k]), k
 
 
-def _delayed_worker(rank, world, trace=False, tp=1):
+def _delayed_worker(rank, world, trace=False, tp=1, trace_device="gpu", break_trace=False):
     import smdistributed_modelparallel_b200 as smp
 
     conf = {"pipeline_parallel_degree": 2, "microbatches": 2, "ddp": tp > 1, "delayed_parameter_initialization": True,
@@ -294,8 +294,14 @@ def _delayed_worker(rank, world, trace=False, tp=1):
     with smp.model_creation(tensor_parallelism=tp > 1):
         module = smp.nn.DistributedTransformerLMHead(**CFG)
     assert all(p.is_meta for p in module.parameters()), "nothing may be materialised before partitioning"
-    model = smp.DistributedModel(module, trace_execution_times=trace, trace_memory_usage=trace)
+    model = smp.DistributedModel(module, trace_execution_times=trace, trace_memory_usage=trace,
+                                 trace_device=trace_device)
     opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.1))
+    if break_trace:
+        def boom(mod, args):
+            if smp.is_tracing():
+                raise RuntimeError("this module cannot run in the traced pass")
+        module.transformer.seq_layers[0].register_forward_pre_hook(boom)
 
     @smp.step
     def train_step(model, ids):
@@ -346,6 +352,20 @@ def test_tracing_under_delayed_initialisation(tp):
         assert r["partition"] == res[0]["partition"]
         assert (r["traced"] > 10 and r["trace_time"] > 0) if r["pp_rank"] == 0 else r["traced"] == 0, r
     assert set(res[0]["partition"].values()) == {0, 1}
+
+
+def test_tracing_on_the_host_and_a_trace_that_fails():
+    """``trace_device="cpu"`` runs the traced passes on borrowed host storage; a traced pass that raises does not end
+    the job - the model is partitioned from the untraced estimates and training goes on."""
+    host = run_distributed(_delayed_worker, 2, True, 1, "cpu", timeout=420)
+    broken = run_distributed(_delayed_worker, 2, True, 1, "gpu", True, timeout=420)
+    for r in host:
+        assert r["meta_left"] == 0 and r["losses"][-1] < r["losses"][0]
+        assert (r["traced"] > 10 and r["trace_time"] > 0) if r["pp_rank"] == 0 else r["traced"] == 0, r
+    for r in broken:
+        assert r["meta_left"] == 0 and r["losses"][-1] < r["losses"][0]
+        assert r["trace_time"] == 0                      # nothing of the failed trace is used
+        assert r["partition"] == broken[0]["partition"] and set(r["partition"].values()) == {0, 1}
 
 
 def _pp_optshard_worker(rank, world):
