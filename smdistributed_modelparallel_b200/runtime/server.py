@@ -283,7 +283,7 @@ class PipelineP2P:
         return buf
 
     # ------------------------------------------------------------------ static mode
-    def begin_step(self, key):
+    def begin_step(self, key, schedule_settled=True):
         cfg = self.state.cfg
         if self._pool_step[0] or self._pool_step[1]:
             self.state.core.pool_record(-self._pool_step[0], -self._pool_step[1], ok=True)
@@ -291,7 +291,11 @@ class PipelineP2P:
         # posting ahead needs the order of receptions from each source to repeat exactly.  It does when stages
         # only answer the leader; with fast-mode chains over three or more stages a stage is fed by two sources and
         # the order of its answers depends on timing, so the dynamic protocol stays in charge there.
-        self._static = bool(getattr(cfg, "static_mode", False)) and not (
+        # ... and it does only once the leader's schedule is final: while warm-up depths are still being tried
+        # (SMP_SCHEDULE_RECORD_STEPS) every step orders its receptions differently, so nothing is recorded or
+        # replayed until the choice is made (the reference, too, registers the receptions of the step it picked,
+        # torch/server_queue.py:596-606)
+        self._static = bool(getattr(cfg, "static_mode", False)) and schedule_settled and not (
             getattr(cfg, "fast_mode", False) and self.state.core.pp_size() > 2)
         if not self._static:
             return
@@ -526,6 +530,7 @@ class ExecutionServer:
         self._orig_forward = {}
         self._early = []                   # control messages that arrived while waiting for the partition
         self._tuners = {}                  # (step function id, grad enabled) -> _ScheduleTuner
+        self._steps_of = {}                # (step function id, grad enabled) -> steps run so far (every rank)
         self.record_steps = int(os.environ.get("SMP_SCHEDULE_RECORD_STEPS", "0"))
 
     # ================================================================== partitioning (first step)
@@ -1099,7 +1104,14 @@ class ExecutionServer:
         if not self.partitioned:
             self._partition(step_fn, args, kwargs, num_mb)
         self._done_msg = None
-        self.p2p.begin_step((st.current_step_func_id, torch.is_grad_enabled(), num_mb))
+        key = (st.current_step_func_id, torch.is_grad_enabled(), num_mb)
+        # every rank counts the steps of a step function the way the leaders' tuner does (runs with and without
+        # gradients apart): the schedule is final from step ``record_steps + 1`` on
+        seen = self._steps_of.get(key[:2], 0)
+        self._steps_of[key[:2]] = seen + 1
+        tuning = (self.record_steps > 0 and self.core.pp_size() >= 2 and st.cfg.pipeline == "interleaved"
+                  and int(st.cfg.active_microbatches) >= 2 and seen <= self.record_steps)
+        self.p2p.begin_step(key, schedule_settled=not tuning)
         pipe = st.pipeline
         pipe.init_step()
         group = self.core.get_pp_group()
