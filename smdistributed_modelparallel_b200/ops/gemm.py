@@ -162,9 +162,16 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
         if _pad_state["ok"] and tri == 0 and _misaligned_only(a, b, out, residual, bias):
             Ap, Bp = aligned_operands(a, b, a_mn_major, b_mn_major)
             if _native_ok(Ap, Bp, out, residual, bias):
-                res = gemm(Ap, Bp, out=out, out_dtype=out_dtype, bias=bias, residual=residual, alpha=alpha, beta=beta,
-                           epilogue=epi, aux_out=aux_out)
-                if not _pad_state["checked"] and residual is not out:
+                try:
+                    res = gemm(Ap, Bp, out=out, out_dtype=out_dtype, bias=bias, residual=residual, alpha=alpha,
+                               beta=beta, epilogue=epi, aux_out=aux_out)
+                except RuntimeError as e:            # the kernel refused the re-packed problem: say so, stay on matmul
+                    from ..backend.logger import get_logger
+                    get_logger().error(f"re-packed GEMM refused by the native kernel ({e}); odd-shaped GEMMs use "
+                                       "torch.matmul from now on")
+                    _pad_state["ok"] = False
+                    res = None
+                if res is not None and not _pad_state["checked"] and residual is not out:
                     # first use in this process (with inputs the call did not overwrite): hold the re-packed path
                     # against the fp32 formulation once; on disagreement say so and stay on torch.matmul
                     _pad_state["checked"] = True
