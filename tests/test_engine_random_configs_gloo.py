@@ -1,6 +1,6 @@
 """Random combinations of engine options on four gloo ranks - pipeline degree 2 / 4, tensor-parallel degree 1 / 2,
 microbatch count and window, ``simple`` / ``interleaved`` schedule, fast mode, static mode, activation checkpointing
-strategy, prescaled batch, schedule tuning - each trained for three SGD steps and compared, loss by loss, with the
+strategy, prescaled batch, schedule tuning, optimizer-state sharding, reducer overlap - each trained for three SGD steps and compared, loss by loss, with the
 dense model on the union batch.  Options are not independent in the engine (fast-mode chains change who talks to whom,
 static mode replays receptions, checkpointing re-runs forwards inside backward ...), so they are exercised together.
 ``SMP_RANDOM_ENGINE_SEEDS=a-b`` widens the search."""
@@ -29,7 +29,10 @@ def options(seed):
     if o["pipeline"] == "interleaved":
         o["active_microbatches"] = rng.choice([mb, max(1, mb // 2), min(mb, pp + 1)])
     extra = {"ckpt": rng.choice([None, None, "each", "contiguous", "group_2"]),
-             "record_steps": rng.choice([0, 0, 2]), "delayed": rng.random() < 0.3}
+             "record_steps": rng.choice([0, 0, 2]), "delayed": rng.random() < 0.3,
+             "overlap": rng.random() < 0.7}
+    if 4 // (pp * tp) > 1 and rng.random() < 0.5:
+        o["shard_optimizer_state"] = True
     if extra["delayed"]:
         o["delayed_parameter_initialization"] = True
     return o, extra
@@ -49,7 +52,7 @@ def _worker(rank, world, seed):
         module = smp.nn.DistributedTransformerLMHead(**CFG)
     if extra["ckpt"]:
         smp.set_activation_checkpointing(module.transformer.seq_layers, pack_args_as_tuple=True, strategy=extra["ckpt"])
-    model = smp.DistributedModel(module)
+    model = smp.DistributedModel(module, overlapping_allreduce=extra["overlap"])
     opt = smp.DistributedOptimizer(torch.optim.SGD(model.parameters(), lr=0.2))
 
     @smp.step
